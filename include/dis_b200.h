@@ -1,0 +1,183 @@
+/*
+ * include/dis_b200.h — C ABI of the B200-native Dense Inverse Search engine.
+ *
+ * This is the drop-in boundary for the reference's hot path.  The reference has no FFI: its
+ * boundary is the C++ class API.  Each entry point below names the reference
+ * interface it replaces (paths relative to /root/reference).  Plain pointers and sizes only; no
+ * C++/torch types; every function returns DIS_OK (0) or a negative dis_status and records a
+ * message retrievable with dis_last_error().  No exceptions cross this boundary.
+ *
+ * There is NO CPU fallback: every compute entry point runs hand-written sm_100a kernels and
+ * fails with DIS_ERR_CUDA when no usable device is present.
+ *
+ * Threading: a handle is used by one host thread at a time; it owns one CUDA stream and all the
+ * device memory it allocates.
+ */
+#ifndef DIS_B200_H
+#define DIS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define DIS_API __attribute__((visibility("default")))
+#else
+#define DIS_API
+#endif
+
+typedef enum dis_status {
+  DIS_OK = 0,
+  DIS_ERR_PARAM = -1,    /* invalid parameter / size (the reference would read out of bounds) */
+  DIS_ERR_CUDA = -2,     /* CUDA runtime error, or no sm_100 device */
+  DIS_ERR_STATE = -3,    /* call sequence error (e.g. results queried before a run) */
+  DIS_ERR_ALLOC = -4
+} dis_status;
+
+/* The parameters of src/main.cpp:63-72 (same names, same defaults via dis_default_params):
+ * max_iter=1000, patch_size=8, coarsest_scale=3, finest_scale=0, patch_overlap=0.7f,
+ * patch_norm=1.  draw_grid is a GUI path and is not part of this ABI. */
+typedef struct dis_params {
+  int max_iter;          /* `iterations`: a patch runs max_iter+1 passes unless it is reset (src/patch.cpp:199) */
+  int patch_size;        /* even, >= 4 */
+  int coarsest_scale;
+  int finest_scale;
+  float patch_overlap;   /* steps = max(1, floor(patch_size*(1-overlap))) in fp32 (src/optical_flow.cpp:38) */
+  int patch_norm;        /* mean-normalise the sampled patch (src/patch.cpp:264) */
+  /* Extension, off by default (0): stop a patch once |delta_u| < conv_eps.  The reference has no
+   * convergence criterion; conv_eps > 0 is a reported deviation, never the default. */
+  float conv_eps;
+  int reserved[5];
+} dis_params;
+
+typedef struct dis_engine dis_engine;   /* opaque handle */
+
+/* Geometry of one level (src/optical_flow.cpp:49-59, src/patch_grid.cpp:20-25). */
+typedef struct dis_level_info {
+  int scale;             /* absolute scale */
+  int width, height;     /* level size */
+  int tmp_w, tmp_h;      /* padded plane size */
+  int npw, nph;          /* patch grid */
+  int offw, offh;        /* grid offsets */
+  int steps;
+  int num_patches;
+} dis_level_info;
+
+/* Counters of the last run (summed over pairs and levels). */
+typedef struct dis_stats {
+  unsigned long long patches;           /* patches processed */
+  unsigned long long patch_iterations;  /* passes of the reference loop accounted for (src/patch.cpp:165-202) */
+  unsigned long long sampled_iterations;/* passes for which the 4-tap resample + reductions actually ran */
+  unsigned long long resets;            /* patches reset to their initial u (src/patch.cpp:185-194) */
+  unsigned long long start_oob;         /* patches whose start was out of bounds (src/patch.cpp:131-138) */
+  unsigned long long kernel_launches;   /* kernels launched by the last run */
+  unsigned long long reserved[2];
+} dis_stats;
+
+DIS_API void dis_default_params(dis_params* p);
+DIS_API const char* dis_last_error(void);
+DIS_API const char* dis_version(void);
+
+/* Handle life cycle.  `device` is a CUDA ordinal. */
+DIS_API int dis_create(const dis_params* p, int device, dis_engine** out);
+DIS_API void dis_destroy(dis_engine* e);
+
+/* ---- whole path, host buffers -----------------------------------------------------------
+ * Replaces the body of the per-pair loop, src/main.cpp:135-198: divisibility pad (:139-155),
+ * u8->f32 (:158-160), construct_pyramide x2 (:177-178, :12-50), the OpticalFlowClass constructor
+ * (:184-189), the finest_scale epilogue (:192-196) and the crop (:198).
+ * a, b: u8 grey frames h x w with row stride `stride` bytes.  flow_out: h x w x 2 fp32 (u,v). */
+DIS_API int dis_run_pair_u8(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, int h,
+                            int stride, float* flow_out);
+
+/* n_pairs independent pairs (BASELINE config 3).  a[i], b[i] frames as above; flow_out holds
+ * n_pairs consecutive h x w x 2 fields. */
+DIS_API int dis_run_batch_u8(dis_engine* e, const uint8_t* const* a, const uint8_t* const* b,
+                             int n_pairs, int w, int h, int stride, float* flow_out);
+
+/* A frame sequence, src/main.cpp:102 loop (frame_i, frame_i+1): n_frames frames stored
+ * contiguously (frame_stride bytes apart) give n_frames-1 flows.  Pyramids are built once per
+ * frame and shared by the two pairs that use it. */
+DIS_API int dis_run_sequence_u8(dis_engine* e, const uint8_t* frames, int n_frames, int w, int h,
+                                int stride, size_t frame_stride, float* flow_out);
+
+/* ---- the exact OpticalFlowClass contract ---------------------------------------------------
+ * Replaces OpticalFlow::OpticalFlowClass::OpticalFlowClass (include/optical_flow.hpp:43-54,
+ * src/optical_flow.cpp:19-132) with draw_grid = false.  Six HOST pyramids indexed by absolute
+ * scale 0..coarsest, planes (height>>s + 2*img_padding) x (width>>s + 2*img_padding) fp32.
+ * Only img_first_dx/dy and img_second are read (the reference never reads the others on this
+ * path); those three may be NULL.  outflow: 2*(width>>finest)*(height>>finest). */
+DIS_API int dis_run_pyramids(dis_engine* e, const float* const* img_first,
+                             const float* const* img_first_dx, const float* const* img_first_dy,
+                             const float* const* img_second, const float* const* img_second_dx,
+                             const float* const* img_second_dy, int img_padding, float* outflow,
+                             int width, int height);
+
+/* ---- construct_pyramide on the device (src/main.cpp:12-50) ---------------------------------
+ * img: fp32 host frame width x height (already divisibility padded).  Writes lv_f+1 padded host
+ * planes per pyramid, as the reference's float** outputs. */
+DIS_API int dis_construct_pyramid(dis_engine* e, const float* img, int width, int height, int lv_f,
+                                  int img_padding, float* const* img_pyr, float* const* img_dx_pyr,
+                                  float* const* img_dy_pyr);
+
+/* ---- device-resident pipeline (what bench.py's `value` times) ------------------------------
+ * upload: copies n_frames u8 frames to the device and defines the pairs (first[i], second[i])
+ * as indices into them.  run: pyramids + all levels for all pairs, asynchronously on the
+ * handle's stream.  download: copies cropped flows (n_pairs x h x w x 2) to the host. */
+DIS_API int dis_upload_frames_u8(dis_engine* e, const uint8_t* frames, int n_frames, int w, int h,
+                                 int stride, size_t frame_stride, const int* first,
+                                 const int* second, int n_pairs);
+DIS_API int dis_run_resident(dis_engine* e);
+DIS_API int dis_download_flows(dis_engine* e, float* flow_out);
+DIS_API int dis_synchronize(dis_engine* e);
+/* CUDA-event timing on the handle's own stream. */
+DIS_API int dis_timer_start(dis_engine* e);
+DIS_API int dis_timer_stop_ms(dis_engine* e, float* ms);
+/* Device time spent in the inverse-search kernels during the last dis_run_resident (events around
+ * each launch), and the number of such launches. */
+DIS_API int dis_last_search_ms(dis_engine* e, float* ms, int* launches);
+
+/* ---- introspection for the parity harness ---------------------------------------------------
+ * Valid after any run; `pair` indexes the pairs of that run, `level` = scale - finest_scale. */
+DIS_API int dis_num_levels(dis_engine* e);
+DIS_API int dis_get_level_info(dis_engine* e, int level, dis_level_info* out);
+/* PatchGrid::get_patch_ref_pos / Patch::get_u_vector / counter_iter for every patch of a level
+ * (include/patch_grid.hpp:28-30, include/patch.hpp:41-43).  Any output may be NULL. */
+DIS_API int dis_get_patches(dis_engine* e, int pair, int level, float* ref_xy, float* u_xy,
+                            int* iters);
+/* The level's dense flow (flows[s] of src/optical_flow.cpp:86-90), height x width x 2. */
+DIS_API int dis_get_level_flow(dis_engine* e, int pair, int level, float* flow);
+/* Padded pyramid planes of one frame of the last run: which = 0 image, 1 dx, 2 dy. */
+DIS_API int dis_get_plane(dis_engine* e, int frame, int scale, int which, float* out);
+DIS_API int dis_get_stats(dis_engine* e, dis_stats* out);
+
+/* ---- PatchGrid-level API (include/patch_grid.hpp:16-30) --------------------------------------
+ * A grid is one level of one pair with host-pointer inputs, mirroring the reference's methods
+ * one to one; used by the C++ mirror classes in include/dis_b200.hpp. */
+typedef struct dis_grid dis_grid;
+DIS_API int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_grid** out);
+DIS_API void dis_grid_destroy(dis_grid* g);
+DIS_API int dis_grid_init(dis_grid* g, const float* img_first, const float* img_first_dx,
+                          const float* img_first_dy);                     /* init_grid */
+DIS_API int dis_grid_set_target(dis_grid* g, const float* img_second, const float* img_second_dx,
+                                const float* img_second_dy);              /* set_target_image */
+DIS_API int dis_grid_init_from_prev_flow(dis_grid* g, const float* flow_prev); /* patch_init_from_prev_flow */
+DIS_API int dis_grid_set_patch_init(dis_grid* g, int i, float ux, float uy);   /* Patch::inverse_search(init) */
+DIS_API int dis_grid_inverse_search(dis_grid* g);                         /* inverse_search */
+DIS_API int dis_grid_densify(dis_grid* g, float* dense_flow);             /* densification_and_create_dance_flow */
+DIS_API int dis_grid_num_patches(dis_grid* g);                            /* get_num_all_patch */
+DIS_API int dis_grid_get_patch(dis_grid* g, int i, float* ref_xy, float* u_xy); /* get_patch_ref_pos / get_u_vector */
+
+/* ---- "next" rows of SURVEY.md §8f ---------------------------------------------------------- */
+/* Middlebury .flo writer/reader, src/IO_flow.cpp:10-98 (tag "PIEH", int32 w, h, interleaved f32). */
+DIS_API int dis_write_flo(const char* path, const float* flow, int w, int h);
+DIS_API int dis_read_flo(const char* path, float* flow, int w, int h);
+DIS_API int dis_read_flo_size(const char* path, int* w, int* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIS_B200_H */

@@ -1,0 +1,830 @@
+// dis_api.cu — the C ABI of include/dis_b200.h: handle, device memory, level loop.
+//
+// Host-side orchestration of the path the reference runs inside the OpticalFlowClass constructor
+// (src/optical_flow.cpp:19-132) and around it in main() (src/main.cpp:135-198).  Everything that
+// computes is a kernel in dis_pyramid.cu / dis_search.cu / dis_densify.cu; there is no CPU path.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/dis_b200.h"
+#include "dis_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t _e = (call);                                                              \
+    if (_e != cudaSuccess)                                                                \
+      return fail(DIS_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e));      \
+  } while (0)
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return -1; }
+    cap = bytes;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct Level {            // one entry per scale finest..coarsest, index s = scale - finest
+  dis_level_info info;
+  float lb, ub_w, ub_h;
+  size_t flow_stride;     // floats per pair
+  DevBuf flow, u, iters;
+};
+
+}  // namespace
+
+struct dis_engine {
+  dis_params prm;
+  int device = 0;
+  int steps = 1;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::vector<cudaEvent_t> search_ev;   // pairs of events around each search launch
+  int search_launches = 0;
+
+  // geometry of the current run
+  int w0 = 0, h0 = 0, W = 0, H = 0, left = 0, top = 0, pad = 0;
+  int n_frames = 0, n_pairs = 0, stride_u8 = 0;
+  bool have_run = false;
+  bool stats_fetched = false;
+  bool keep_iters = true;
+
+  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters;
+  dis::LevelPlanes planes[16];          // by absolute scale
+  size_t plane_elems[16];
+  std::vector<Level> levels;
+  dis_stats stats;
+  unsigned long long launches = 0;
+};
+
+namespace {
+
+int check_params(const dis_params& p) {
+  if (p.patch_size < 4 || (p.patch_size & 1) || p.patch_size > 16 || p.patch_size == 14)
+    return fail(DIS_ERR_PARAM, "patch_size must be one of 4, 6, 8, 10, 12, 16 (odd sizes are broken in the reference, SURVEY.md F9)");
+  if (p.coarsest_scale < p.finest_scale || p.finest_scale < 0 || p.coarsest_scale > 15)
+    return fail(DIS_ERR_PARAM, "need 0 <= finest_scale <= coarsest_scale <= 15");
+  if (p.max_iter < 0) return fail(DIS_ERR_PARAM, "max_iter must be >= 0");
+  if (!(p.patch_overlap >= 0.f && p.patch_overlap < 1.f)) return fail(DIS_ERR_PARAM, "patch_overlap must be in [0,1)");
+  return DIS_OK;
+}
+
+// src/optical_flow.cpp:38
+int steps_of(int ps, float overlap) {
+  const float one_minus = 1 - overlap;
+  const int s = (int)floorf((float)ps * one_minus);
+  return std::max(1, s);
+}
+
+// (Re)define the geometry of a run and size every device buffer.  W,H: level-0 size after the
+// divisibility padding; pad: img_padding.
+int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
+  const dis_params& p = e->prm;
+  const int sf = 1 << p.coarsest_scale;
+  if (W <= 0 || H <= 0 || (W % sf) || (H % sf))
+    return fail(DIS_ERR_PARAM, "width/height must be positive multiples of 2^coarsest_scale");
+  if (pad < p.patch_size) return fail(DIS_ERR_PARAM, "img_padding must be >= patch_size");
+  if ((W >> p.coarsest_scale) < 2 || (H >> p.coarsest_scale) < 2)
+    return fail(DIS_ERR_PARAM, "coarsest level would be smaller than 2x2");
+  if (n_frames < 1 || n_pairs < 1) return fail(DIS_ERR_PARAM, "need at least one frame and one pair");
+  e->W = W; e->H = H; e->pad = pad; e->n_frames = n_frames; e->n_pairs = n_pairs;
+  // planes for ALL scales 0..coarsest (construct_pyramide builds every level, src/main.cpp:177)
+  size_t total = 0;
+  size_t off[16];
+  for (int s = 0; s <= p.coarsest_scale; ++s) {
+    const size_t tw = (W >> s) + 2 * pad, th = (H >> s) + 2 * pad;
+    e->plane_elems[s] = (tw * th + 3) & ~(size_t)3;
+    off[s] = total;
+    total += 3 * e->plane_elems[s] * (size_t)n_frames;
+  }
+  if (e->planes_all.ensure(total * sizeof(float))) return fail(DIS_ERR_ALLOC, "cudaMalloc(planes) failed");
+  for (int s = 0; s <= p.coarsest_scale; ++s) {
+    e->planes[s].base = e->planes_all.as<float>() + off[s];
+    e->planes[s].plane_stride = e->plane_elems[s];
+    e->planes[s].frame_stride = 3 * e->plane_elems[s];
+  }
+  const int nl = p.coarsest_scale - p.finest_scale + 1;
+  e->levels.resize(nl);
+  for (int s = 0; s < nl; ++s) {
+    Level& L = e->levels[s];
+    const int scale = p.finest_scale + s;
+    dis_level_info& I = L.info;
+    const float sc = (float)pow(2, -scale);            // src/optical_flow.cpp:51-59
+    I.scale = scale;
+    I.height = (int)(H * sc);
+    I.width = (int)(W * sc);
+    I.tmp_w = I.width + 2 * pad;
+    I.tmp_h = I.height + 2 * pad;
+    I.steps = e->steps;
+    L.lb = -(float)p.patch_size / 2;
+    L.ub_w = (float)(I.width + p.patch_size / 2 - 2);
+    L.ub_h = (float)(I.height + p.patch_size / 2 - 2);
+    I.npw = (int)ceilf((float)I.width / (float)I.steps);   // src/patch_grid.cpp:20-23
+    I.nph = (int)ceilf((float)I.height / (float)I.steps);
+    I.offw = (I.width - (I.npw - 1) * I.steps) / 2;
+    I.offh = (I.height - (I.nph - 1) * I.steps) / 2;
+    I.num_patches = I.npw * I.nph;
+    L.flow_stride = 2 * (size_t)I.width * I.height;
+    if (L.flow.ensure(L.flow_stride * n_pairs * sizeof(float)) ||
+        L.u.ensure(2 * (size_t)I.num_patches * n_pairs * sizeof(float)) ||
+        L.iters.ensure((size_t)I.num_patches * n_pairs * sizeof(int)))
+      return fail(DIS_ERR_ALLOC, "cudaMalloc(level buffers) failed");
+  }
+  if (e->pairs.ensure(sizeof(int2) * (size_t)n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(pairs) failed");
+  if (e->counters.ensure(sizeof(unsigned long long) * 4)) return fail(DIS_ERR_ALLOC, "cudaMalloc(counters) failed");
+  return DIS_OK;
+}
+
+}  // namespace
+
+namespace {
+
+// The coarse-to-fine loop of src/optical_flow.cpp:67-90 for all pairs of the run, on e->stream.
+int run_levels(dis_engine* e) {
+  const dis_params& p = e->prm;
+  const int nl = (int)e->levels.size();
+  CU(cudaMemsetAsync(e->counters.p, 0, 4 * sizeof(unsigned long long), e->stream));
+  while ((int)e->search_ev.size() < 2 * nl) {
+    cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev);
+  }
+  e->search_launches = 0;
+  unsigned long long patches = 0;
+  for (int s = nl - 1; s >= 0; --s) {
+    Level& L = e->levels[s];
+    const dis_level_info& I = L.info;
+    dis::SearchArgs a;
+    memset(&a, 0, sizeof a);
+    a.planes = e->planes[I.scale];
+    a.pairs = e->pairs.as<int2>();
+    a.flow_prev = (s < nl - 1) ? e->levels[s + 1].flow.as<float>() : nullptr;
+    a.flow_prev_stride = (s < nl - 1) ? e->levels[s + 1].flow_stride : 0;
+    a.init_override = nullptr;
+    a.u_out = L.u.as<float>();
+    a.iters_out = e->keep_iters ? L.iters.as<int>() : nullptr;
+    a.counters = e->counters.as<unsigned long long>();
+    a.n_pairs = e->n_pairs;
+    a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
+    a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
+    a.warps_per_pair = (I.num_patches + 31) / 32;
+    a.iterations = p.max_iter; a.patnorm = p.patch_norm ? 1 : 0;
+    a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
+    a.outlier = (float)p.patch_size / 2;               // src/optical_flow.cpp:34
+    a.conv_eps = p.conv_eps;
+    CU(cudaEventRecord(e->search_ev[2 * e->search_launches], e->stream));
+    const int n = dis::launch_inverse_search(a, p.patch_size, e->stream);
+    if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
+    CU(cudaEventRecord(e->search_ev[2 * e->search_launches + 1], e->stream));
+    e->search_launches++;
+    e->launches += n;
+    dis::DensifyArgs d;
+    d.u = L.u.as<float>(); d.dense = L.flow.as<float>(); d.dense_stride = L.flow_stride;
+    d.n_pairs = e->n_pairs; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
+    d.offw = I.offw; d.offh = I.offh; d.steps = I.steps; d.np = I.num_patches; d.ps = p.patch_size;
+    e->launches += dis::launch_densify(d, e->stream);
+    patches += (unsigned long long)I.num_patches * e->n_pairs;
+  }
+  CU(cudaGetLastError());
+  e->stats.patches = patches;
+  e->have_run = true;
+  e->stats_fetched = false;
+  return DIS_OK;
+}
+
+int fetch_counters(dis_engine* e) {
+  unsigned long long c[4];
+  CU(cudaMemcpyAsync(c, e->counters.p, sizeof c, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  e->stats.patch_iterations = c[0]; e->stats.sampled_iterations = c[1];
+  e->stats.resets = c[2]; e->stats.start_oob = c[3];
+  e->stats.kernel_launches = e->launches;
+  e->stats_fetched = true;
+  return DIS_OK;
+}
+
+int run_pyramid_u8(dis_engine* e, int stride) {
+  dis::PyramidArgs a;
+  memset(&a, 0, sizeof a);
+  a.frames = e->frames_u8.as<uint8_t>();
+  a.frame_stride_bytes = (size_t)stride * e->h0;
+  a.stride0 = stride; a.w0 = e->w0; a.h0 = e->h0;
+  a.W = e->W; a.H = e->H; a.left = e->left; a.top = e->top;
+  a.n_frames = e->n_frames; a.levels = e->prm.coarsest_scale + 1; a.pad = e->pad;
+  for (int s = 0; s <= e->prm.coarsest_scale; ++s) a.planes[s] = e->planes[s];
+  e->launches += dis::launch_pyramid(a, e->stream);
+  CU(cudaGetLastError());
+  return DIS_OK;
+}
+
+// finest dense flow -> cropped output (src/main.cpp:192-198), device to device
+int run_epilogue(dis_engine* e) {
+  Level& L = e->levels[0];
+  if (e->out.ensure(sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
+  if (e->prm.finest_scale == 0)
+    e->launches += dis::launch_crop(L.flow.as<float>(), L.flow_stride, L.info.width, L.info.height, e->left, e->top,
+                                    e->out.as<float>(), e->w0, e->h0, e->n_pairs, e->stream);
+  else
+    e->launches += dis::launch_upsample_crop(L.flow.as<float>(), L.flow_stride, L.info.width, L.info.height,
+                                             e->prm.finest_scale, e->left, e->top, e->out.as<float>(), e->w0, e->h0,
+                                             e->n_pairs, e->stream);
+  CU(cudaGetLastError());
+  return DIS_OK;
+}
+
+int div_pad(int dim, int coarsest) {   // src/main.cpp:139-149
+  const int sf = 1 << coarsest, r = dim % sf;
+  return r > 0 ? sf - r : 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+void dis_default_params(dis_params* p) {   // src/main.cpp:63-72
+  if (!p) return;
+  memset(p, 0, sizeof *p);
+  p->max_iter = 1000; p->patch_size = 8; p->coarsest_scale = 3; p->finest_scale = 0;
+  p->patch_overlap = 0.7f; p->patch_norm = 1; p->conv_eps = 0.f;
+}
+
+const char* dis_last_error(void) { return g_err.c_str(); }
+const char* dis_version(void) { return "dis_b200 0.1 (sm_100a)"; }
+
+int dis_create(const dis_params* p, int device, dis_engine** out) {
+  if (!p || !out) return fail(DIS_ERR_PARAM, "null argument");
+  *out = nullptr;
+  if (int rc = check_params(*p)) return rc;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return fail(DIS_ERR_CUDA, "no CUDA device: this engine has no CPU path");
+  }
+  if (device < 0 || device >= n) return fail(DIS_ERR_PARAM, "device ordinal out of range");
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(DIS_ERR_CUDA, "kernels are built for sm_100a only");
+  CU(cudaSetDevice(device));
+  dis_engine* e = new dis_engine();
+  e->prm = *p; e->device = device;
+  e->steps = steps_of(p->patch_size, p->patch_overlap);
+  memset(&e->stats, 0, sizeof e->stats);
+  if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess) {
+    delete e;
+    return fail(DIS_ERR_CUDA, "stream/event creation failed");
+  }
+  *out = e;
+  return DIS_OK;
+}
+
+void dis_destroy(dis_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (Level& L : e->levels) { L.flow.release(); L.u.release(); L.iters.release(); }
+  e->frames_u8.release(); e->frames_f32.release(); e->pairs.release(); e->planes_all.release();
+  e->out.release(); e->counters.release();
+  for (cudaEvent_t ev : e->search_ev) cudaEventDestroy(ev);
+  if (e->ev0) cudaEventDestroy(e->ev0);
+  if (e->ev1) cudaEventDestroy(e->ev1);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int dis_upload_frames_u8(dis_engine* e, const uint8_t* frames, int n_frames, int w, int h, int stride,
+                         size_t frame_stride, const int* first, const int* second, int n_pairs) {
+  if (!e || !frames || !first || !second) return fail(DIS_ERR_PARAM, "null argument");
+  if (w <= 0 || h <= 0 || stride < w || frame_stride < (size_t)stride * h) return fail(DIS_ERR_PARAM, "bad frame geometry");
+  CU(cudaSetDevice(e->device));
+  const int padw = div_pad(w, e->prm.coarsest_scale), padh = div_pad(h, e->prm.coarsest_scale);
+  e->w0 = w; e->h0 = h; e->left = padw / 2; e->top = padh / 2;
+  if (int rc = setup_run(e, w + padw, h + padh, e->prm.patch_size, n_frames, n_pairs)) return rc;
+  std::vector<int2> pr(n_pairs);
+  for (int i = 0; i < n_pairs; ++i) {
+    if (first[i] < 0 || first[i] >= n_frames || second[i] < 0 || second[i] >= n_frames)
+      return fail(DIS_ERR_PARAM, "pair index out of range");
+    pr[i] = make_int2(first[i], second[i]);
+  }
+  const size_t fbytes = (size_t)stride * h;
+  if (e->frames_u8.ensure(fbytes * n_frames)) return fail(DIS_ERR_ALLOC, "cudaMalloc(frames) failed");
+  if (frame_stride == fbytes) {
+    CU(cudaMemcpyAsync(e->frames_u8.p, frames, fbytes * n_frames, cudaMemcpyHostToDevice, e->stream));
+  } else {
+    CU(cudaMemcpy2DAsync(e->frames_u8.p, fbytes, frames, frame_stride, fbytes, n_frames, cudaMemcpyHostToDevice, e->stream));
+  }
+  CU(cudaMemcpyAsync(e->pairs.p, pr.data(), sizeof(int2) * n_pairs, cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));   // pr is a host temporary
+  e->stride_u8 = stride;
+  e->have_run = false;
+  return DIS_OK;
+}
+
+int dis_run_resident(dis_engine* e) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->frames_u8.p || e->n_pairs <= 0) return fail(DIS_ERR_STATE, "dis_upload_frames_u8 first");
+  CU(cudaSetDevice(e->device));
+  e->launches = 0;
+  if (int rc = run_pyramid_u8(e, e->stride_u8)) return rc;
+  if (int rc = run_levels(e)) return rc;
+  return run_epilogue(e);
+}
+
+int dis_download_flows(dis_engine* e, float* flow_out) {
+  if (!e || !flow_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run to download");
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(flow_out, e->out.p, sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs,
+                     cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_synchronize(dis_engine* e) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_timer_start(dis_engine* e) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  CU(cudaEventRecord(e->ev0, e->stream));
+  return DIS_OK;
+}
+
+int dis_timer_stop_ms(dis_engine* e, float* ms) {
+  if (!e || !ms) return fail(DIS_ERR_PARAM, "null argument");
+  CU(cudaEventRecord(e->ev1, e->stream));
+  CU(cudaEventSynchronize(e->ev1));
+  CU(cudaEventElapsedTime(ms, e->ev0, e->ev1));
+  return DIS_OK;
+}
+
+int dis_last_search_ms(dis_engine* e, float* ms, int* launches) {
+  if (!e || !ms) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  CU(cudaStreamSynchronize(e->stream));
+  float total = 0.f;
+  for (int i = 0; i < e->search_launches; ++i) {
+    float t = 0.f;
+    CU(cudaEventElapsedTime(&t, e->search_ev[2 * i], e->search_ev[2 * i + 1]));
+    total += t;
+  }
+  *ms = total;
+  if (launches) *launches = e->search_launches;
+  return DIS_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// host-buffer entry points
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kMaxChunkPairs = 128;   // bounds device memory per chunk (~18 MB per Sintel pair)
+
+// Upload `n_frames` separately addressed frames, run everything, download the cropped flows.
+int run_frames(dis_engine* e, const uint8_t* const* fptr, int n_frames, int w, int h, int stride,
+               const int* first, const int* second, int n_pairs, float* flow_out) {
+  CU(cudaSetDevice(e->device));
+  const int padw = div_pad(w, e->prm.coarsest_scale), padh = div_pad(h, e->prm.coarsest_scale);
+  e->w0 = w; e->h0 = h; e->left = padw / 2; e->top = padh / 2;
+  if (int rc = setup_run(e, w + padw, h + padh, e->prm.patch_size, n_frames, n_pairs)) return rc;
+  const size_t fbytes = (size_t)w * h;   // frames are stored densely on the device
+  if (e->frames_u8.ensure(fbytes * n_frames)) return fail(DIS_ERR_ALLOC, "cudaMalloc(frames) failed");
+  for (int f = 0; f < n_frames; ++f)
+    CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>() + fbytes * f, w, fptr[f], stride, w, h,
+                         cudaMemcpyHostToDevice, e->stream));
+  std::vector<int2> pr(n_pairs);
+  for (int i = 0; i < n_pairs; ++i) pr[i] = make_int2(first[i], second[i]);
+  CU(cudaMemcpyAsync(e->pairs.p, pr.data(), sizeof(int2) * n_pairs, cudaMemcpyHostToDevice, e->stream));
+  e->stride_u8 = w;
+  e->launches = 0;
+  if (int rc = run_pyramid_u8(e, w)) return rc;
+  if (int rc = run_levels(e)) return rc;
+  if (int rc = run_epilogue(e)) return rc;
+  CU(cudaMemcpyAsync(flow_out, e->out.p, sizeof(float) * 2 * fbytes * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  return fetch_counters(e);   // synchronises; pr stays alive until here
+}
+
+void add_stats(dis_stats* acc, const dis_stats& s) {
+  acc->patches += s.patches; acc->patch_iterations += s.patch_iterations;
+  acc->sampled_iterations += s.sampled_iterations; acc->resets += s.resets;
+  acc->start_oob += s.start_oob; acc->kernel_launches += s.kernel_launches;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dis_run_pair_u8(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, int h, int stride, float* flow_out) {
+  if (!e || !a || !b || !flow_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (w <= 0 || h <= 0 || stride < w) return fail(DIS_ERR_PARAM, "bad frame geometry");
+  const uint8_t* f[2] = {a, b};
+  const int first = 0, second = 1;
+  return run_frames(e, f, 2, w, h, stride, &first, &second, 1, flow_out);
+}
+
+int dis_run_batch_u8(dis_engine* e, const uint8_t* const* a, const uint8_t* const* b, int n_pairs, int w, int h,
+                     int stride, float* flow_out) {
+  if (!e || !a || !b || !flow_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (n_pairs <= 0 || w <= 0 || h <= 0 || stride < w) return fail(DIS_ERR_PARAM, "bad batch geometry");
+  dis_stats acc; memset(&acc, 0, sizeof acc);
+  std::vector<const uint8_t*> f;
+  std::vector<int> fi, se;
+  for (int base = 0; base < n_pairs; base += kMaxChunkPairs) {
+    const int n = std::min(kMaxChunkPairs, n_pairs - base);
+    f.resize(2 * n); fi.resize(n); se.resize(n);
+    for (int i = 0; i < n; ++i) {
+      if (!a[base + i] || !b[base + i]) return fail(DIS_ERR_PARAM, "null frame pointer");
+      f[2 * i] = a[base + i]; f[2 * i + 1] = b[base + i]; fi[i] = 2 * i; se[i] = 2 * i + 1;
+    }
+    if (int rc = run_frames(e, f.data(), 2 * n, w, h, stride, fi.data(), se.data(), n,
+                            flow_out + (size_t)base * 2 * w * h)) return rc;
+    add_stats(&acc, e->stats);
+  }
+  if (n_pairs > kMaxChunkPairs) e->stats = acc;
+  return DIS_OK;
+}
+
+int dis_run_sequence_u8(dis_engine* e, const uint8_t* frames, int n_frames, int w, int h, int stride,
+                        size_t frame_stride, float* flow_out) {
+  if (!e || !frames || !flow_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (n_frames < 2 || w <= 0 || h <= 0 || stride < w || frame_stride < (size_t)stride * h)
+    return fail(DIS_ERR_PARAM, "bad sequence geometry");
+  dis_stats acc; memset(&acc, 0, sizeof acc);
+  std::vector<const uint8_t*> f;
+  std::vector<int> fi, se;
+  const int n_pairs = n_frames - 1;
+  for (int base = 0; base < n_pairs; base += kMaxChunkPairs) {
+    const int n = std::min(kMaxChunkPairs, n_pairs - base);
+    f.resize(n + 1); fi.resize(n); se.resize(n);
+    for (int i = 0; i <= n; ++i) f[i] = frames + frame_stride * (size_t)(base + i);
+    for (int i = 0; i < n; ++i) { fi[i] = i; se[i] = i + 1; }
+    if (int rc = run_frames(e, f.data(), n + 1, w, h, stride, fi.data(), se.data(), n,
+                            flow_out + (size_t)base * 2 * w * h)) return rc;
+    add_stats(&acc, e->stats);
+  }
+  if (n_pairs > kMaxChunkPairs) e->stats = acc;
+  return DIS_OK;
+}
+
+int dis_run_pyramids(dis_engine* e, const float* const* img_first, const float* const* img_first_dx,
+                     const float* const* img_first_dy, const float* const* img_second,
+                     const float* const* img_second_dx, const float* const* img_second_dy, int img_padding,
+                     float* outflow, int width, int height) {
+  (void)img_first; (void)img_second_dx; (void)img_second_dy;   // never read on this path
+  if (!e || !img_first_dx || !img_first_dy || !img_second || !outflow) return fail(DIS_ERR_PARAM, "null argument");
+  CU(cudaSetDevice(e->device));
+  e->w0 = width; e->h0 = height; e->left = 0; e->top = 0;
+  if (int rc = setup_run(e, width, height, img_padding, 2, 1)) return rc;
+  const int2 pr = make_int2(0, 1);
+  CU(cudaMemcpyAsync(e->pairs.p, &pr, sizeof pr, cudaMemcpyHostToDevice, e->stream));
+  for (const Level& L : e->levels) {
+    const int s = L.info.scale;
+    if (!img_first_dx[s] || !img_first_dy[s] || !img_second[s]) return fail(DIS_ERR_PARAM, "null pyramid plane");
+    const size_t bytes = sizeof(float) * (size_t)L.info.tmp_w * L.info.tmp_h;
+    const dis::LevelPlanes& P = e->planes[s];
+    CU(cudaMemcpyAsync(P.base + P.plane_stride, img_first_dx[s], bytes, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(P.base + 2 * P.plane_stride, img_first_dy[s], bytes, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(P.base + P.frame_stride, img_second[s], bytes, cudaMemcpyHostToDevice, e->stream));
+  }
+  e->launches = 0;
+  if (int rc = run_levels(e)) return rc;
+  const Level& F = e->levels[0];
+  CU(cudaMemcpyAsync(outflow, F.flow.p, sizeof(float) * F.flow_stride, cudaMemcpyDeviceToHost, e->stream));
+  return fetch_counters(e);
+}
+
+int dis_construct_pyramid(dis_engine* e, const float* img, int width, int height, int lv_f, int img_padding,
+                          float* const* img_pyr, float* const* img_dx_pyr, float* const* img_dy_pyr) {
+  if (!e || !img || !img_pyr || !img_dx_pyr || !img_dy_pyr) return fail(DIS_ERR_PARAM, "null argument");
+  if (lv_f < 0 || lv_f > 15) return fail(DIS_ERR_PARAM, "lv_f out of range");
+  CU(cudaSetDevice(e->device));
+  const dis_params saved = e->prm;
+  e->prm.coarsest_scale = lv_f; e->prm.finest_scale = 0;
+  e->w0 = width; e->h0 = height; e->left = 0; e->top = 0;
+  int rc = setup_run(e, width, height, img_padding, 1, 1);
+  if (rc == DIS_OK && e->frames_f32.ensure(sizeof(float) * (size_t)width * height)) rc = fail(DIS_ERR_ALLOC, "cudaMalloc failed");
+  if (rc != DIS_OK) { e->prm = saved; e->levels.clear(); return rc; }
+  auto body = [&]() -> int {
+    CU(cudaMemcpyAsync(e->frames_f32.p, img, sizeof(float) * (size_t)width * height, cudaMemcpyHostToDevice, e->stream));
+    dis::PyramidArgs a;
+    memset(&a, 0, sizeof a);
+    a.frames = nullptr; a.frames_f32 = e->frames_f32.as<float>();
+    a.W = width; a.H = height; a.n_frames = 1; a.levels = lv_f + 1; a.pad = img_padding;
+    for (int s = 0; s <= lv_f; ++s) a.planes[s] = e->planes[s];
+    e->launches = dis::launch_pyramid(a, e->stream);
+    CU(cudaGetLastError());
+    for (int s = 0; s <= lv_f; ++s) {
+      const size_t bytes = sizeof(float) * (size_t)((width >> s) + 2 * img_padding) * ((height >> s) + 2 * img_padding);
+      const dis::LevelPlanes& P = e->planes[s];
+      if (img_pyr[s]) CU(cudaMemcpyAsync(img_pyr[s], P.base, bytes, cudaMemcpyDeviceToHost, e->stream));
+      if (img_dx_pyr[s]) CU(cudaMemcpyAsync(img_dx_pyr[s], P.base + P.plane_stride, bytes, cudaMemcpyDeviceToHost, e->stream));
+      if (img_dy_pyr[s]) CU(cudaMemcpyAsync(img_dy_pyr[s], P.base + 2 * P.plane_stride, bytes, cudaMemcpyDeviceToHost, e->stream));
+    }
+    CU(cudaStreamSynchronize(e->stream));
+    return DIS_OK;
+  };
+  rc = body();
+  e->prm = saved;
+  e->levels.clear();       // geometry no longer matches the engine's own parameters
+  e->have_run = false;
+  return rc;
+}
+
+// ---- introspection ---------------------------------------------------------------------------
+int dis_num_levels(dis_engine* e) { return e ? (int)e->levels.size() : 0; }
+
+int dis_get_level_info(dis_engine* e, int level, dis_level_info* out) {
+  if (!e || !out) return fail(DIS_ERR_PARAM, "null argument");
+  if (level < 0 || level >= (int)e->levels.size()) return fail(DIS_ERR_PARAM, "level out of range");
+  *out = e->levels[level].info;
+  return DIS_OK;
+}
+
+int dis_get_patches(dis_engine* e, int pair, int level, float* ref_xy, float* u_xy, int* iters) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  if (level < 0 || level >= (int)e->levels.size() || pair < 0 || pair >= e->n_pairs) return fail(DIS_ERR_PARAM, "index out of range");
+  const Level& L = e->levels[level];
+  const dis_level_info& I = L.info;
+  CU(cudaSetDevice(e->device));
+  if (ref_xy) {   // src/patch_grid.cpp:39-49
+    int id = 0;
+    for (int x = 0; x < I.npw; ++x)
+      for (int y = 0; y < I.nph; ++y, ++id) {
+        ref_xy[2 * id] = (float)(x * I.steps + I.offw);
+        ref_xy[2 * id + 1] = (float)(y * I.steps + I.offh);
+      }
+  }
+  if (u_xy) CU(cudaMemcpyAsync(u_xy, L.u.as<float>() + 2 * (size_t)I.num_patches * pair, sizeof(float) * 2 * I.num_patches, cudaMemcpyDeviceToHost, e->stream));
+  if (iters) {
+    if (!e->keep_iters) return fail(DIS_ERR_STATE, "iteration counts were not kept");
+    CU(cudaMemcpyAsync(iters, L.iters.as<int>() + (size_t)I.num_patches * pair, sizeof(int) * I.num_patches, cudaMemcpyDeviceToHost, e->stream));
+  }
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_get_level_flow(dis_engine* e, int pair, int level, float* flow) {
+  if (!e || !flow) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  if (level < 0 || level >= (int)e->levels.size() || pair < 0 || pair >= e->n_pairs) return fail(DIS_ERR_PARAM, "index out of range");
+  const Level& L = e->levels[level];
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(flow, L.flow.as<float>() + L.flow_stride * pair, sizeof(float) * L.flow_stride, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_get_plane(dis_engine* e, int frame, int scale, int which, float* out) {
+  if (!e || !out) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  if (frame < 0 || frame >= e->n_frames || scale < 0 || scale > e->prm.coarsest_scale || which < 0 || which > 2)
+    return fail(DIS_ERR_PARAM, "index out of range");
+  const dis::LevelPlanes& P = e->planes[scale];
+  const size_t n = (size_t)((e->W >> scale) + 2 * e->pad) * ((e->H >> scale) + 2 * e->pad);
+  CU(cudaSetDevice(e->device));
+  CU(cudaMemcpyAsync(out, P.base + P.frame_stride * frame + P.plane_stride * which, sizeof(float) * n, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_get_stats(dis_engine* e, dis_stats* out) {
+  if (!e || !out) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  CU(cudaSetDevice(e->device));
+  if (!e->stats_fetched)
+    if (int rc = fetch_counters(e)) return rc;
+  *out = e->stats;
+  return DIS_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// PatchGrid-level API (include/patch_grid.hpp:16-30): one level of one pair, host pointers
+// ---------------------------------------------------------------------------------------------
+struct dis_grid {
+  dis_engine* e;
+  dis_level_info info;
+  int pad;
+  float lb, ub_w, ub_h;
+  size_t plane_elems;
+  DevBuf planes, flow_prev, init, u, dense, pair;
+  std::vector<float> init_host;
+  bool have_first = false, have_second = false, use_prev = false, use_override = false, searched = false;
+  std::vector<float> u_host;
+};
+
+extern "C" {
+
+int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_grid** out) {
+  if (!e || !out) return fail(DIS_ERR_PARAM, "null argument");
+  *out = nullptr;
+  if (width < 2 || height < 2) return fail(DIS_ERR_PARAM, "level too small");
+  if (img_padding < e->prm.patch_size) return fail(DIS_ERR_PARAM, "img_padding must be >= patch_size");
+  CU(cudaSetDevice(e->device));
+  dis_grid* g = new dis_grid();
+  g->e = e; g->pad = img_padding;
+  dis_level_info& I = g->info;
+  const int ps = e->prm.patch_size;
+  I.scale = 0; I.width = width; I.height = height;
+  I.tmp_w = width + 2 * img_padding; I.tmp_h = height + 2 * img_padding;
+  I.steps = e->steps;
+  I.npw = (int)ceilf((float)width / (float)I.steps);
+  I.nph = (int)ceilf((float)height / (float)I.steps);
+  I.offw = (width - (I.npw - 1) * I.steps) / 2;
+  I.offh = (height - (I.nph - 1) * I.steps) / 2;
+  I.num_patches = I.npw * I.nph;
+  g->lb = -(float)ps / 2; g->ub_w = (float)(width + ps / 2 - 2); g->ub_h = (float)(height + ps / 2 - 2);
+  g->plane_elems = ((size_t)I.tmp_w * I.tmp_h + 3) & ~(size_t)3;
+  const int2 pr = make_int2(0, 1);
+  if (g->planes.ensure(sizeof(float) * 6 * g->plane_elems) || g->u.ensure(sizeof(float) * 2 * I.num_patches) ||
+      g->dense.ensure(sizeof(float) * 2 * (size_t)width * height) || g->pair.ensure(sizeof(int2)) ||
+      g->init.ensure(sizeof(float) * 2 * I.num_patches) ||
+      g->flow_prev.ensure(sizeof(float) * 2 * (size_t)(width / 2 + 1) * (height / 2 + 1))) {
+    dis_grid_destroy(g);
+    return fail(DIS_ERR_ALLOC, "cudaMalloc(grid) failed");
+  }
+  cudaMemcpy(g->pair.p, &pr, sizeof pr, cudaMemcpyHostToDevice);
+  g->init_host.assign(2 * (size_t)I.num_patches, 0.f);
+  *out = g;
+  return DIS_OK;
+}
+
+void dis_grid_destroy(dis_grid* g) {
+  if (!g) return;
+  cudaSetDevice(g->e->device);
+  cudaStreamSynchronize(g->e->stream);
+  g->planes.release(); g->flow_prev.release(); g->init.release(); g->u.release(); g->dense.release(); g->pair.release();
+  delete g;
+}
+
+int dis_grid_init(dis_grid* g, const float* img_first, const float* dx, const float* dy) {
+  (void)img_first;   // gathered by the reference but never used
+  if (!g || !dx || !dy) return fail(DIS_ERR_PARAM, "null argument");
+  CU(cudaSetDevice(g->e->device));
+  const size_t bytes = sizeof(float) * (size_t)g->info.tmp_w * g->info.tmp_h;
+  float* base = g->planes.as<float>();
+  CU(cudaMemcpyAsync(base + g->plane_elems, dx, bytes, cudaMemcpyHostToDevice, g->e->stream));
+  CU(cudaMemcpyAsync(base + 2 * g->plane_elems, dy, bytes, cudaMemcpyHostToDevice, g->e->stream));
+  CU(cudaStreamSynchronize(g->e->stream));
+  std::fill(g->init_host.begin(), g->init_host.end(), 0.f);   // src/patch_grid.cpp:80
+  g->use_prev = g->use_override = false;
+  g->have_first = true; g->searched = false;
+  return DIS_OK;
+}
+
+int dis_grid_set_target(dis_grid* g, const float* img_second, const float* dx, const float* dy) {
+  (void)dx; (void)dy;   // never read
+  if (!g || !img_second) return fail(DIS_ERR_PARAM, "null argument");
+  CU(cudaSetDevice(g->e->device));
+  const size_t bytes = sizeof(float) * (size_t)g->info.tmp_w * g->info.tmp_h;
+  CU(cudaMemcpyAsync(g->planes.as<float>() + 3 * g->plane_elems, img_second, bytes, cudaMemcpyHostToDevice, g->e->stream));
+  CU(cudaStreamSynchronize(g->e->stream));
+  g->have_second = true; g->searched = false;
+  return DIS_OK;
+}
+
+int dis_grid_init_from_prev_flow(dis_grid* g, const float* flow_prev) {
+  if (!g || !flow_prev) return fail(DIS_ERR_PARAM, "null argument");
+  CU(cudaSetDevice(g->e->device));
+  const size_t n = 2 * (size_t)(g->info.width / 2) * (g->info.height / 2);
+  CU(cudaMemcpyAsync(g->flow_prev.p, flow_prev, sizeof(float) * n, cudaMemcpyHostToDevice, g->e->stream));
+  CU(cudaStreamSynchronize(g->e->stream));
+  g->use_prev = true; g->use_override = false;
+  return DIS_OK;
+}
+
+int dis_grid_set_patch_init(dis_grid* g, int i, float ux, float uy) {
+  if (!g) return fail(DIS_ERR_PARAM, "null grid");
+  if (i < 0 || i >= g->info.num_patches) return fail(DIS_ERR_PARAM, "patch index out of range");
+  if (g->use_prev) return fail(DIS_ERR_STATE, "explicit inits cannot be mixed with init_from_prev_flow");
+  g->init_host[2 * i] = ux; g->init_host[2 * i + 1] = uy;
+  g->use_override = true;
+  return DIS_OK;
+}
+
+int dis_grid_inverse_search(dis_grid* g) {
+  if (!g) return fail(DIS_ERR_PARAM, "null grid");
+  if (!g->have_first || !g->have_second) return fail(DIS_ERR_STATE, "init_grid and set_target_image first");
+  dis_engine* e = g->e;
+  CU(cudaSetDevice(e->device));
+  const dis_level_info& I = g->info;
+  if (g->use_override)
+    CU(cudaMemcpyAsync(g->init.p, g->init_host.data(), sizeof(float) * 2 * I.num_patches, cudaMemcpyHostToDevice, e->stream));
+  dis::SearchArgs a;
+  memset(&a, 0, sizeof a);
+  a.planes.base = g->planes.as<float>(); a.planes.plane_stride = g->plane_elems; a.planes.frame_stride = 3 * g->plane_elems;
+  a.pairs = g->pair.as<int2>();
+  a.flow_prev = g->use_prev ? g->flow_prev.as<float>() : nullptr;
+  a.init_override = g->use_override ? g->init.as<float>() : nullptr;
+  a.u_out = g->u.as<float>();
+  a.n_pairs = 1;
+  a.width = I.width; a.height = I.height; a.pad = g->pad; a.tmp_w = I.tmp_w;
+  a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
+  a.warps_per_pair = (I.num_patches + 31) / 32;
+  a.iterations = e->prm.max_iter; a.patnorm = e->prm.patch_norm ? 1 : 0;
+  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.outlier = (float)e->prm.patch_size / 2;
+  a.conv_eps = e->prm.conv_eps;
+  if (dis::launch_inverse_search(a, e->prm.patch_size, e->stream) < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
+  CU(cudaGetLastError());
+  g->u_host.resize(2 * (size_t)I.num_patches);
+  CU(cudaMemcpyAsync(g->u_host.data(), g->u.p, sizeof(float) * 2 * I.num_patches, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  g->searched = true;
+  return DIS_OK;
+}
+
+int dis_grid_densify(dis_grid* g, float* dense_flow) {
+  if (!g || !dense_flow) return fail(DIS_ERR_PARAM, "null argument");
+  if (!g->searched) return fail(DIS_ERR_STATE, "inverse_search first");
+  dis_engine* e = g->e;
+  CU(cudaSetDevice(e->device));
+  const dis_level_info& I = g->info;
+  dis::DensifyArgs d;
+  d.u = g->u.as<float>(); d.dense = g->dense.as<float>(); d.dense_stride = 2 * (size_t)I.width * I.height;
+  d.n_pairs = 1; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
+  d.offw = I.offw; d.offh = I.offh; d.steps = I.steps; d.np = I.num_patches; d.ps = e->prm.patch_size;
+  dis::launch_densify(d, e->stream);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(dense_flow, g->dense.p, sizeof(float) * d.dense_stride, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_grid_num_patches(dis_grid* g) { return g ? g->info.num_patches : 0; }
+
+int dis_grid_get_patch(dis_grid* g, int i, float* ref_xy, float* u_xy) {
+  if (!g) return fail(DIS_ERR_PARAM, "null grid");
+  if (i < 0 || i >= g->info.num_patches) return fail(DIS_ERR_PARAM, "patch index out of range");
+  const dis_level_info& I = g->info;
+  if (ref_xy) {
+    ref_xy[0] = (float)((i / I.nph) * I.steps + I.offw);
+    ref_xy[1] = (float)((i % I.nph) * I.steps + I.offh);
+  }
+  if (u_xy) {
+    if (g->searched) { u_xy[0] = g->u_host[2 * i]; u_xy[1] = g->u_host[2 * i + 1]; }
+    else { u_xy[0] = 0.f; u_xy[1] = 0.f; }   // Patch::reset_patch, src/patch.cpp:102-116
+  }
+  return DIS_OK;
+}
+
+// ---- Middlebury .flo (src/IO_flow.cpp:10-98) ----------------------------------------------------
+int dis_write_flo(const char* path, const float* flow, int w, int h) {
+  if (!path || !flow || w <= 0 || h <= 0) return fail(DIS_ERR_PARAM, "bad argument");
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(DIS_ERR_PARAM, std::string("cannot open ") + path);
+  const int32_t wh[2] = {w, h};
+  bool ok = fwrite("PIEH", 1, 4, f) == 4 && fwrite(wh, sizeof(int32_t), 2, f) == 2 &&
+            fwrite(flow, sizeof(float), 2 * (size_t)w * h, f) == 2 * (size_t)w * h;
+  fclose(f);
+  return ok ? DIS_OK : fail(DIS_ERR_PARAM, "short write");
+}
+
+int dis_read_flo_size(const char* path, int* w, int* h) {
+  if (!path || !w || !h) return fail(DIS_ERR_PARAM, "bad argument");
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(DIS_ERR_PARAM, std::string("cannot open ") + path);
+  char tag[4]; int32_t wh[2];
+  bool ok = fread(tag, 1, 4, f) == 4 && fread(wh, sizeof(int32_t), 2, f) == 2 && memcmp(tag, "PIEH", 4) == 0;
+  fclose(f);
+  if (!ok) return fail(DIS_ERR_PARAM, "not a .flo file");
+  *w = wh[0]; *h = wh[1];
+  return DIS_OK;
+}
+
+int dis_read_flo(const char* path, float* flow, int w, int h) {
+  int fw = 0, fh = 0;
+  if (int rc = dis_read_flo_size(path, &fw, &fh)) return rc;
+  if (!flow || fw != w || fh != h) return fail(DIS_ERR_PARAM, "size mismatch");
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(DIS_ERR_PARAM, std::string("cannot open ") + path);
+  fseek(f, 12, SEEK_SET);
+  const size_t n = 2 * (size_t)w * h;
+  const bool ok = fread(flow, sizeof(float), n, f) == n;
+  fclose(f);
+  return ok ? DIS_OK : fail(DIS_ERR_PARAM, "file too short");
+}
+
+}  // extern "C"

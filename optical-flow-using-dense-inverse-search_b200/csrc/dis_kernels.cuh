@@ -1,0 +1,73 @@
+// dis_kernels.cuh — shared declarations of the sm_100a kernels behind include/dis_b200.h.
+//
+// Arithmetic contract: fp32, IEEE round-to-nearest, expressions in the
+// reference's association, NO FMA contraction.  The whole library is compiled with
+// -fmad=false -prec-div=true -prec-sqrt=true -ftz=false; `+ - * / sqrtf floorf ceilf fabsf`
+// are then bit-identical to the SSE2 scalar operations of the CPU reference.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dis {
+
+// Planes of one pyramid level for all frames of a run, in HBM:
+//   base + frame*frame_stride + which*plane_stride + y*tmp_w + x     (which: 0 image, 1 dx, 2 dy)
+// Each plane is the reference's padded plane (src/main.cpp:41-49): (h+2*pad) x (w+2*pad),
+// replicate border for the image, zero border for the gradients.
+struct LevelPlanes {
+  float* base;
+  size_t frame_stride;   // floats
+  size_t plane_stride;   // floats
+};
+
+// Everything one level of the inverse search needs (image_parameters + fix_parameters of
+// include/optical_flow.hpp:14-37 and the grid geometry of src/patch_grid.cpp:20-25).
+struct SearchArgs {
+  LevelPlanes planes;
+  const int2* pairs;        // (first frame, second frame) per pair
+  const float* flow_prev;   // coarser dense flow [pair][h/2][w/2][2], or nullptr at the coarsest level
+  size_t flow_prev_stride;  // floats per pair
+  const float* init_override; // optional explicit per-patch init [pair][np][2] (PatchGrid API); else nullptr
+  float* u_out;             // [pair][np][2]
+  int* iters_out;           // [pair][np] or nullptr
+  unsigned long long* counters;  // [4]: patch_iterations, sampled_iterations, resets, start_oob (or nullptr)
+  int n_pairs;
+  int width, height, pad, tmp_w;
+  int npw, nph, offw, offh, steps, np;
+  int warps_per_pair;
+  int iterations, patnorm;
+  float lb, ub_w, ub_h, outlier;
+  float conv_eps;           // 0 = off (reference behaviour)
+};
+
+struct DensifyArgs {
+  const float* u;           // [pair][np][2]
+  float* dense;             // [pair][h][w][2]
+  size_t dense_stride;      // floats per pair
+  int n_pairs, width, height, npw, nph, offw, offh, steps, np, ps;
+};
+
+// host-callable launchers (each returns the number of kernels launched)
+int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s);
+int launch_densify(const DensifyArgs& a, cudaStream_t s);
+
+struct PyramidArgs {
+  const uint8_t* frames;    // [frame][h0][stride0] u8 (un-padded input frames), or nullptr if f32 input
+  const float* frames_f32;  // [frame][H][W] fp32 (already divisibility padded) when frames == nullptr
+  size_t frame_stride_bytes;
+  int stride0, w0, h0;      // input geometry (u8 path)
+  int W, H;                 // level-0 size after divisibility padding
+  int left, top;            // divisibility padding split (src/main.cpp:152)
+  int n_frames, levels, pad;
+  LevelPlanes planes[16];
+};
+int launch_pyramid(const PyramidArgs& a, cudaStream_t s);
+
+// crop the divisibility padding of the finest dense flow into the output layout
+int launch_crop(const float* dense, size_t dense_stride, int W, int H, int left, int top, float* out,
+                int w, int h, int n_pairs, cudaStream_t s);
+// finest_scale > 0 epilogue (src/main.cpp:192-198): flow * 2^f, bilinear x2^f upsample, crop
+int launch_upsample_crop(const float* dense, size_t dense_stride, int Wf, int Hf, int finest, int left,
+                         int top, float* out, int w, int h, int n_pairs, cudaStream_t s);
+
+}  // namespace dis

@@ -1,0 +1,252 @@
+"""ctypes binding of the C ABI in include/dis_b200.h (libdis_b200.so, hand-written sm_100a kernels).
+
+This is the Python face of the product path: it only marshals pointers.  There is no CPU
+implementation behind it — if the library is missing or no B200 is visible every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdis_b200.so")
+
+_u8p = C.POINTER(C.c_uint8)
+_fp = C.POINTER(C.c_float)
+_ip = C.POINTER(C.c_int)
+
+
+class DisParams(C.Structure):
+    """dis_params — the parameters of /root/reference/src/main.cpp:63-72."""
+    _fields_ = [("max_iter", C.c_int), ("patch_size", C.c_int), ("coarsest_scale", C.c_int),
+                ("finest_scale", C.c_int), ("patch_overlap", C.c_float), ("patch_norm", C.c_int),
+                ("conv_eps", C.c_float), ("reserved", C.c_int * 5)]
+
+
+class DisLevelInfo(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("scale", "width", "height", "tmp_w", "tmp_h", "npw", "nph", "offw", "offh",
+                                       "steps", "num_patches")]
+
+
+class DisStats(C.Structure):
+    _fields_ = [(n, C.c_ulonglong) for n in ("patches", "patch_iterations", "sampled_iterations", "resets",
+                                             "start_oob", "kernel_launches")] + [("reserved", C.c_ulonglong * 2)]
+
+
+class DisError(RuntimeError):
+    pass
+
+
+_lib = None
+
+# every symbol include/dis_b200.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "dis_default_params", "dis_last_error", "dis_version", "dis_create", "dis_destroy", "dis_run_pair_u8",
+    "dis_run_batch_u8", "dis_run_sequence_u8", "dis_run_pyramids", "dis_construct_pyramid", "dis_upload_frames_u8",
+    "dis_run_resident", "dis_download_flows", "dis_synchronize", "dis_timer_start", "dis_timer_stop_ms",
+    "dis_last_search_ms", "dis_num_levels", "dis_get_level_info", "dis_get_patches", "dis_get_level_flow",
+    "dis_get_plane", "dis_get_stats", "dis_grid_create", "dis_grid_destroy", "dis_grid_init", "dis_grid_set_target",
+    "dis_grid_init_from_prev_flow", "dis_grid_set_patch_init", "dis_grid_inverse_search", "dis_grid_densify",
+    "dis_grid_num_patches", "dis_grid_get_patch", "dis_write_flo", "dis_read_flo", "dis_read_flo_size",
+]
+
+
+def load_library() -> C.CDLL:
+    """Load libdis_b200.so; raise loudly when it was not built (no fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise DisError(f"{LIB_PATH} not built: run __graft_entry__.build() (make -C csrc); there is no CPU fallback")
+        lib = C.CDLL(LIB_PATH)
+        lib.dis_last_error.restype = C.c_char_p
+        lib.dis_version.restype = C.c_char_p
+        lib.dis_destroy.restype = None
+        lib.dis_grid_destroy.restype = None
+        lib.dis_destroy.argtypes = [C.c_void_p]
+        lib.dis_grid_destroy.argtypes = [C.c_void_p]
+        _lib = lib
+    return _lib
+
+
+def _chk(rc: int) -> None:
+    if rc != 0:
+        raise DisError(f"dis error {rc}: {load_library().dis_last_error().decode()}")
+
+
+def default_params(**kw) -> DisParams:
+    p = DisParams()
+    load_library().dis_default_params(C.byref(p))
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise TypeError(f"unknown parameter {k}")
+        setattr(p, k, v)
+    return p
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+class Engine:
+    """One dis_engine handle (one CUDA stream, one device)."""
+
+    def __init__(self, device: int = 0, **params):
+        self.lib = load_library()
+        self.params = default_params(**params)
+        self._h = C.c_void_p()
+        _chk(self.lib.dis_create(C.byref(self.params), int(device), C.byref(self._h)))
+        self._shape = None
+
+    def close(self):
+        if self._h:
+            self.lib.dis_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- whole path, host buffers ---------------------------------------------------------
+    def run_pair(self, a: np.ndarray, b: np.ndarray) -> np.ndarray:
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        assert a.ndim == 2 and a.shape == b.shape
+        h, w = a.shape
+        out = np.empty((h, w, 2), np.float32)
+        _chk(self.lib.dis_run_pair_u8(self._h, a.ctypes.data_as(_u8p), b.ctypes.data_as(_u8p), w, h, w,
+                                      out.ctypes.data_as(_fp)))
+        return out
+
+    def run_batch(self, a: np.ndarray, b: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        n, h, w = a.shape
+        if out is None:
+            out = np.empty((n, h, w, 2), np.float32)
+        pa = (C.c_void_p * n)(*[a.ctypes.data + i * h * w for i in range(n)])
+        pb = (C.c_void_p * n)(*[b.ctypes.data + i * h * w for i in range(n)])
+        _chk(self.lib.dis_run_batch_u8(self._h, pa, pb, n, w, h, w, out.ctypes.data_as(_fp)))
+        return out
+
+    def run_sequence(self, frames: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n, h, w = frames.shape
+        if out is None:
+            out = np.empty((n - 1, h, w, 2), np.float32)
+        _chk(self.lib.dis_run_sequence_u8(self._h, frames.ctypes.data_as(_u8p), n, w, h, w, C.c_size_t(h * w),
+                                          out.ctypes.data_as(_fp)))
+        return out
+
+    def run_sequence_ptr(self, frames_ptr: int, n: int, w: int, h: int, out_ptr: int) -> None:
+        """Same as run_sequence on raw (e.g. pinned) host addresses."""
+        _chk(self.lib.dis_run_sequence_u8(self._h, C.cast(C.c_void_p(frames_ptr), _u8p), n, w, h, w, C.c_size_t(h * w),
+                                          C.cast(C.c_void_p(out_ptr), _fp)))
+
+    # ---- the OpticalFlowClass contract ------------------------------------------------------
+    def run_pyramids(self, pyr_first, pyr_second, img_padding: int, width: int, height: int) -> np.ndarray:
+        """pyr_* = (img, dx, dy) lists indexed by absolute scale (padded fp32 planes)."""
+        def arr(planes):
+            keep = [None if p is None else _f32(p) for p in planes]
+            ptrs = (C.c_void_p * len(keep))(*[None if p is None else p.ctypes.data for p in keep])
+            return keep, ptrs
+        keep, six = [], []
+        for planes in (*pyr_first, *pyr_second):
+            k, p = arr(planes)
+            keep.append(k); six.append(p)
+        f = self.params.finest_scale
+        out = np.empty((height >> f, width >> f, 2), np.float32)
+        _chk(self.lib.dis_run_pyramids(self._h, *six, int(img_padding), out.ctypes.data_as(_fp), int(width), int(height)))
+        return out
+
+    def construct_pyramid(self, img: np.ndarray, lv_f: int, img_padding: int):
+        img = _f32(img)
+        H, W = img.shape
+        mk = lambda: [np.empty(((H >> i) + 2 * img_padding, (W >> i) + 2 * img_padding), np.float32) for i in range(lv_f + 1)]
+        P, Px, Py = mk(), mk(), mk()
+        ptr = lambda L: (C.c_void_p * len(L))(*[x.ctypes.data for x in L])
+        _chk(self.lib.dis_construct_pyramid(self._h, img.ctypes.data_as(_fp), W, H, int(lv_f), int(img_padding),
+                                            ptr(P), ptr(Px), ptr(Py)))
+        return P, Px, Py
+
+    # ---- device-resident pipeline -------------------------------------------------------------
+    def upload_frames(self, frames: np.ndarray, first, second) -> None:
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n, h, w = frames.shape
+        first = np.ascontiguousarray(first, np.int32); second = np.ascontiguousarray(second, np.int32)
+        _chk(self.lib.dis_upload_frames_u8(self._h, frames.ctypes.data_as(_u8p), n, w, h, w, C.c_size_t(h * w),
+                                           first.ctypes.data_as(_ip), second.ctypes.data_as(_ip), len(first)))
+        self._shape = (len(first), h, w)
+
+    def run_resident(self) -> None:
+        _chk(self.lib.dis_run_resident(self._h))
+
+    def download_flows(self, out: np.ndarray | None = None) -> np.ndarray:
+        n, h, w = self._shape
+        if out is None:
+            out = np.empty((n, h, w, 2), np.float32)
+        _chk(self.lib.dis_download_flows(self._h, out.ctypes.data_as(_fp)))
+        return out
+
+    def synchronize(self) -> None:
+        _chk(self.lib.dis_synchronize(self._h))
+
+    def timer_start(self) -> None:
+        _chk(self.lib.dis_timer_start(self._h))
+
+    def timer_stop_ms(self) -> float:
+        ms = C.c_float()
+        _chk(self.lib.dis_timer_stop_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def last_search_ms(self):
+        ms, n = C.c_float(), C.c_int()
+        _chk(self.lib.dis_last_search_ms(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    # ---- introspection ------------------------------------------------------------------------
+    def num_levels(self) -> int:
+        return self.lib.dis_num_levels(self._h)
+
+    def level_info(self, level: int) -> dict:
+        li = DisLevelInfo()
+        _chk(self.lib.dis_get_level_info(self._h, level, C.byref(li)))
+        return {n: getattr(li, n) for n, _ in DisLevelInfo._fields_}
+
+    def patches(self, pair: int, level: int):
+        n = self.level_info(level)["num_patches"]
+        ref = np.empty((n, 2), np.float32); u = np.empty((n, 2), np.float32); it = np.empty(n, np.int32)
+        _chk(self.lib.dis_get_patches(self._h, pair, level, ref.ctypes.data_as(_fp), u.ctypes.data_as(_fp),
+                                      it.ctypes.data_as(_ip)))
+        return ref, u, it
+
+    def level_flow(self, pair: int, level: int) -> np.ndarray:
+        li = self.level_info(level)
+        out = np.empty((li["height"], li["width"], 2), np.float32)
+        _chk(self.lib.dis_get_level_flow(self._h, pair, level, out.ctypes.data_as(_fp)))
+        return out
+
+    def plane(self, frame: int, scale: int, which: int, shape) -> np.ndarray:
+        out = np.empty(shape, np.float32)
+        _chk(self.lib.dis_get_plane(self._h, frame, scale, which, out.ctypes.data_as(_fp)))
+        return out
+
+    def stats(self) -> dict:
+        s = DisStats()
+        _chk(self.lib.dis_get_stats(self._h, C.byref(s)))
+        return {n: int(getattr(s, n)) for n, _ in DisStats._fields_[:6]}
+
+
+def write_flo(path: str, flow: np.ndarray) -> None:
+    flow = _f32(flow)
+    _chk(load_library().dis_write_flo(path.encode(), flow.ctypes.data_as(_fp), flow.shape[1], flow.shape[0]))
+
+
+def read_flo(path: str) -> np.ndarray:
+    lib = load_library()
+    w, h = C.c_int(), C.c_int()
+    _chk(lib.dis_read_flo_size(path.encode(), C.byref(w), C.byref(h)))
+    out = np.empty((h.value, w.value, 2), np.float32)
+    _chk(lib.dis_read_flo(path.encode(), out.ctypes.data_as(_fp), w.value, h.value))
+    return out
