@@ -139,6 +139,8 @@ DIS_API int dis_timer_stop_ms(dis_engine* e, float* ms);
 /* Device time spent in the inverse-search kernels during the last dis_run_resident (events around
  * each launch), and the number of such launches. */
 DIS_API int dis_last_search_ms(dis_engine* e, float* ms, int* launches);
+/* Same, for the launch of one level (level = scale - finest_scale). */
+DIS_API int dis_last_search_level_ms(dis_engine* e, int level, float* ms);
 
 /* ---- introspection for the parity harness ---------------------------------------------------
  * Valid after any run; `pair` indexes the pairs of that run, `level` = scale - finest_scale. */

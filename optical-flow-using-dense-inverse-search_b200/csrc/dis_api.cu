@@ -377,6 +377,17 @@ int dis_timer_stop_ms(dis_engine* e, float* ms) {
   return DIS_OK;
 }
 
+int dis_last_search_level_ms(dis_engine* e, int level, float* ms) {
+  if (!e || !ms) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  const int nl = (int)e->levels.size();
+  if (level < 0 || level >= nl || e->search_launches != nl) return fail(DIS_ERR_PARAM, "level out of range");
+  CU(cudaStreamSynchronize(e->stream));
+  const int i = nl - 1 - level;   // launches go coarsest -> finest
+  CU(cudaEventElapsedTime(ms, e->search_ev[2 * i], e->search_ev[2 * i + 1]));
+  return DIS_OK;
+}
+
 int dis_last_search_ms(dis_engine* e, float* ms, int* launches) {
   if (!e || !ms) return fail(DIS_ERR_PARAM, "null argument");
   if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
