@@ -68,7 +68,8 @@ struct dis_engine {
   bool stats_fetched = false;
   bool keep_iters = true;
 
-  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters;
+  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers;
+  int straggler_cap = 0;
   dis::LevelPlanes planes[16];          // by absolute scale
   size_t plane_elems[16];
   std::vector<Level> levels;
@@ -151,6 +152,13 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
   }
   if (e->pairs.ensure(sizeof(int2) * (size_t)n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(pairs) failed");
   if (e->counters.ensure(sizeof(unsigned long long) * 4)) return fail(DIS_ERR_ALLOC, "cudaMalloc(counters) failed");
+  // hand-off list of the inverse search (20 bytes per entry + the counter in front)
+  {
+    size_t maxp = 0;
+    for (const Level& L : e->levels) maxp = std::max(maxp, (size_t)L.info.num_patches * n_pairs);
+    e->straggler_cap = (int)std::min<size_t>(maxp / 8 + 4096, (size_t)1 << 28);
+    if (e->stragglers.ensure(64 + (size_t)e->straggler_cap * 20)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stragglers) failed");
+  }
   return DIS_OK;
 }
 
@@ -181,6 +189,9 @@ int run_levels(dis_engine* e) {
     a.u_out = L.u.as<float>();
     a.iters_out = e->keep_iters ? L.iters.as<int>() : nullptr;
     a.counters = e->counters.as<unsigned long long>();
+    a.straggler_count = e->stragglers.as<int>();
+    a.stragglers = e->stragglers.as<char>() + 64;
+    a.straggler_cap = e->straggler_cap;
     a.n_pairs = e->n_pairs;
     a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
     a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
@@ -300,7 +311,7 @@ void dis_destroy(dis_engine* e) {
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (Level& L : e->levels) { L.flow.release(); L.u.release(); L.iters.release(); }
-  e->frames_u8.release(); e->frames_f32.release(); e->pairs.release(); e->planes_all.release();
+  e->frames_u8.release(); e->frames_f32.release(); e->pairs.release(); e->planes_all.release(); e->stragglers.release();
   e->out.release(); e->counters.release();
   for (cudaEvent_t ev : e->search_ev) cudaEventDestroy(ev);
   if (e->ev0) cudaEventDestroy(e->ev0);

@@ -31,6 +31,9 @@ struct SearchArgs {
   float* u_out;             // [pair][np][2]
   int* iters_out;           // [pair][np] or nullptr
   unsigned long long* counters;  // [4]: patch_iterations, sampled_iterations, resets, start_oob (or nullptr)
+  void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
+  int* straggler_count;     // number of entries (device)
+  int straggler_cap;
   int n_pairs;
   int width, height, pad, tmp_w;
   int npw, nph, offw, offh, steps, np;
