@@ -17,6 +17,10 @@ FRAC_PATCH = 0.999
 TOL_DENSE = 0.01     # px, north_star
 
 
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
 @pytest.fixture(scope="module")
 def eng():
     e = dis_b200.Engine(0)
@@ -24,8 +28,16 @@ def eng():
     e.close()
 
 
-def _compare(e, oracle, a, b, **kw):
-    flow_o, d = oracle.run_pair_u8(a, b, dump=True, **{k: v for k, v in kw.items()})
+def _oracle_kw(params):
+    m = {"max_iter": "iterations", "patch_size": "patch_size", "coarsest_scale": "coarsest",
+         "finest_scale": "finest", "patch_overlap": "overlap", "patch_norm": "patnorm"}
+    return {m[k]: v for k, v in params.items() if k in m}
+
+
+def compare_pair(e, oracle, a, b, **params):
+    """Run one pair through engine `e` (created with `params`) and the oracle; assert the north-star
+    bars and the stronger bit-identity, level by level."""
+    flow_o, d = oracle.run_pair_u8(a, b, dump=True, **_oracle_kw(params))
     flow_g = e.run_pair(a, b)
     nl = e.num_levels()
     assert nl == len(d["info"])
@@ -39,18 +51,76 @@ def _compare(e, oracle, a, b, **kw):
         assert np.array_equal(ref, d["ref"][s]), f"grid coordinates differ at level {s}"
         dist = np.linalg.norm(u - d["u"][s], axis=1)
         tot += len(dist); ok += int((dist <= TOL_PATCH).sum())
-        assert np.array_equal(u.view(np.uint32), d["u"][s].view(np.uint32)), \
+        assert np.array_equal(bits(u), bits(d["u"][s])), \
             f"level {s}: {(dist > 0).sum()} of {len(dist)} patches not bit-identical (max {dist.max()})"
         assert np.array_equal(it, d["iters"][s]), f"iteration counts differ at level {s}"
-        assert np.array_equal(e.level_flow(0, s).view(np.uint32), d["flow"][s].view(np.uint32)), f"dense flow differs at level {s}"
+        assert np.array_equal(bits(e.level_flow(0, s)), bits(d["flow"][s])), f"dense flow differs at level {s}"
     assert ok / tot >= FRAC_PATCH
     epd = np.linalg.norm(flow_g - flow_o, axis=-1).mean()
     assert epd <= TOL_DENSE
-    assert np.array_equal(flow_g.view(np.uint32), flow_o.view(np.uint32))
+    assert np.array_equal(bits(flow_g), bits(flow_o))
     return flow_g
 
 
 def test_small_pair_defaults(eng, oracle_port):
     a, b, gt = dis_b200.synth.make_pair(256, 112, seed=0)
-    flow = _compare(eng, oracle_port, a, b)
+    flow = compare_pair(eng, oracle_port, a, b)
     assert np.linalg.norm(flow - gt, axis=-1).mean() < 0.3
+
+
+# sizes that need divisibility padding on one or both axes (src/main.cpp:139-155), a level whose
+# grid y-offset is 0 (h = 55 at scale 3 of 440) and tiny frames
+@pytest.mark.parametrize("w,h,seed", [(250, 107, 1), (264, 120, 2), (131, 77, 3), (64, 48, 4)])
+def test_ragged_sizes(eng, oracle_port, w, h, seed):
+    a, b, _ = dis_b200.synth.make_pair(w, h, seed=seed)
+    compare_pair(eng, oracle_port, a, b)
+
+
+@pytest.mark.parametrize("params", [
+    dict(patch_size=12, patch_overlap=0.75, coarsest_scale=4),   # BASELINE config 4 shape (HQ)
+    dict(patch_size=4, patch_overlap=0.5, coarsest_scale=2),
+    dict(patch_size=6, patch_overlap=0.7, coarsest_scale=2),     # ps^2 % 8 == 4: Eigen's odd packet
+    dict(patch_size=10, patch_overlap=0.6, coarsest_scale=2),
+    dict(patch_size=16, patch_overlap=0.8, coarsest_scale=2),
+    dict(patch_norm=0),
+    dict(max_iter=0), dict(max_iter=1), dict(max_iter=7), dict(max_iter=100),
+    dict(patch_overlap=0.0), dict(patch_overlap=0.95),           # steps = 8 (no overlap) / steps = 1
+    dict(coarsest_scale=0), dict(coarsest_scale=1), dict(coarsest_scale=4),
+])
+def test_parameter_coverage(oracle_port, params):
+    w, h = (480, 272) if params.get("patch_size", 8) == 12 else (192, 96)
+    if params.get("patch_overlap") == 0.95:
+        w, h = 96, 64
+    a, b, _ = dis_b200.synth.make_pair(w, h, seed=5)
+    e = dis_b200.Engine(0, **params)
+    try:
+        compare_pair(e, oracle_port, a, b, **params)
+    finally:
+        e.close()
+
+
+def test_large_motion_resets_and_oob(eng, oracle_port):
+    """Flow amplitude well beyond patch_size/2: many patches are reset (src/patch.cpp:185-194) and
+    some start out of bounds (:131-138); counters must agree with the oracle's iteration counts."""
+    a, b, _ = dis_b200.synth.make_pair(256, 112, seed=6, amp=14.0)
+    compare_pair(eng, oracle_port, a, b)
+    st = eng.stats()
+    assert st["resets"] > 0
+
+
+def test_flat_and_saturated_frames(eng, oracle_port):
+    """det == 0 patches (src/patch.cpp:86-90): constant frames give all-zero gradients, u stays at init."""
+    a = np.full((112, 256), 77, np.uint8)
+    flow = compare_pair(eng, oracle_port, a, a.copy())
+    assert not flow.any()
+    rng = np.random.default_rng(0)
+    c = (rng.random((112, 256)) > 0.5).astype(np.uint8) * 255     # saturated binary noise
+    compare_pair(eng, oracle_port, c, np.roll(c, 1, axis=1))
+
+
+def test_half_flat_frame(eng, oracle_port):
+    """Texture on the left, constant on the right: singular and regular patches side by side."""
+    a, b, _ = dis_b200.synth.make_pair(256, 112, seed=8)
+    a = a.copy(); b = b.copy()
+    a[:, 128:] = 100; b[:, 128:] = 100
+    compare_pair(eng, oracle_port, a, b)
