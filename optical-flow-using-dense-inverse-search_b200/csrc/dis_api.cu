@@ -68,7 +68,7 @@ struct dis_engine {
   bool stats_fetched = false;
   bool keep_iters = true;
 
-  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers;
+  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers, stage;
   int straggler_cap = 0;
   dis::LevelPlanes planes[16];          // by absolute scale
   size_t plane_elems[16];
@@ -87,6 +87,15 @@ int check_params(const dis_params& p) {
   if (p.max_iter < 0) return fail(DIS_ERR_PARAM, "max_iter must be >= 0");
   if (!(p.patch_overlap >= 0.f && p.patch_overlap < 1.f)) return fail(DIS_ERR_PARAM, "patch_overlap must be in [0,1)");
   return DIS_OK;
+}
+
+// Largest fp32 s with sqrtf(s) <= thr.  sqrtf is correctly rounded and monotone, so the reference's
+// `norm() > outlierthresh` (src/patch.cpp:185) is exactly `dx*dx + dy*dy > out2max`.
+float sq_threshold(float thr) {
+  float s = thr * thr;
+  while (sqrtf(s) > thr) s = nextafterf(s, 0.f);
+  while (sqrtf(nextafterf(s, INFINITY)) <= thr) s = nextafterf(s, INFINITY);
+  return s;
 }
 
 // src/optical_flow.cpp:38
@@ -151,7 +160,7 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
       return fail(DIS_ERR_ALLOC, "cudaMalloc(level buffers) failed");
   }
   if (e->pairs.ensure(sizeof(int2) * (size_t)n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(pairs) failed");
-  if (e->counters.ensure(sizeof(unsigned long long) * 4)) return fail(DIS_ERR_ALLOC, "cudaMalloc(counters) failed");
+  if (e->counters.ensure(sizeof(unsigned long long) * 16)) return fail(DIS_ERR_ALLOC, "cudaMalloc(counters) failed");
   // hand-off list of the inverse search (20 bytes per entry + the counter in front)
   {
     size_t maxp = 0;
@@ -170,7 +179,7 @@ namespace {
 int run_levels(dis_engine* e) {
   const dis_params& p = e->prm;
   const int nl = (int)e->levels.size();
-  CU(cudaMemsetAsync(e->counters.p, 0, 4 * sizeof(unsigned long long), e->stream));
+  CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
   while ((int)e->search_ev.size() < 2 * nl) {
     cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev);
   }
@@ -190,6 +199,7 @@ int run_levels(dis_engine* e) {
     a.iters_out = e->keep_iters ? L.iters.as<int>() : nullptr;
     a.counters = e->counters.as<unsigned long long>();
     a.straggler_count = e->stragglers.as<int>();
+    a.work_counter = e->stragglers.as<int>() + 8;
     a.stragglers = e->stragglers.as<char>() + 64;
     a.straggler_cap = e->straggler_cap;
     a.n_pairs = e->n_pairs;
@@ -198,8 +208,8 @@ int run_levels(dis_engine* e) {
     a.warps_per_pair = (I.num_patches + 31) / 32;
     a.iterations = p.max_iter; a.patnorm = p.patch_norm ? 1 : 0;
     a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
-    a.outlier = (float)p.patch_size / 2;               // src/optical_flow.cpp:34
-    a.conv_eps = p.conv_eps;
+    a.out2max = sq_threshold((float)p.patch_size / 2);   // outlierthresh, src/optical_flow.cpp:34
+    a.conv_eps2 = p.conv_eps * p.conv_eps;
     CU(cudaEventRecord(e->search_ev[2 * e->search_launches], e->stream));
     const int n = dis::launch_inverse_search(a, p.patch_size, e->stream);
     if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
@@ -221,9 +231,15 @@ int run_levels(dis_engine* e) {
 }
 
 int fetch_counters(dis_engine* e) {
-  unsigned long long c[4];
+  unsigned long long c[16];
   CU(cudaMemcpyAsync(c, e->counters.p, sizeof c, cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
+#ifdef DIS_DEBUG_STATS
+  fprintf(stderr, "[dis debug] walker warps %llu: chunks/warp %.1f, cycles/warp %.0f | requests/lane %.1f, rtt cycles %.0f | "
+                  "sampler warps %llu: batches/warp %.1f, fill %.2f, busy cycles/batch %.0f, busy share %.3f | running lanes/chunk %.1f\n",
+          c[12], (double)c[4] / c[12], (double)c[5] / c[12], (double)c[11] / (32.0 * c[12]), (double)c[10] / (c[11] ? c[11] : 1),
+          c[13], (double)c[6] / c[13], (double)c[7] / (c[6] ? c[6] : 1), (double)c[8] / (c[6] ? c[6] : 1), (double)c[8] / (c[9] ? c[9] : 1), (double)c[14] / (c[4] ? c[4] : 1));
+#endif
   e->stats.patch_iterations = c[0]; e->stats.sampled_iterations = c[1];
   e->stats.resets = c[2]; e->stats.start_oob = c[3];
   e->stats.kernel_launches = e->launches;
@@ -312,6 +328,7 @@ void dis_destroy(dis_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (Level& L : e->levels) { L.flow.release(); L.u.release(); L.iters.release(); }
   e->frames_u8.release(); e->frames_f32.release(); e->pairs.release(); e->planes_all.release(); e->stragglers.release();
+  e->stage.release();
   e->out.release(); e->counters.release();
   for (cudaEvent_t ev : e->search_ev) cudaEventDestroy(ev);
   if (e->ev0) cudaEventDestroy(e->ev0);
@@ -523,10 +540,13 @@ int dis_run_pyramids(dis_engine* e, const float* const* img_first, const float* 
   for (const Level& L : e->levels) {
     const int s = L.info.scale;
     if (!img_first_dx[s] || !img_first_dy[s] || !img_second[s]) return fail(DIS_ERR_PARAM, "null pyramid plane");
-    const size_t bytes = sizeof(float) * (size_t)L.info.tmp_w * L.info.tmp_h;
+    const size_t n = (size_t)L.info.tmp_w * L.info.tmp_h, bytes = sizeof(float) * n;
     const dis::LevelPlanes& P = e->planes[s];
-    CU(cudaMemcpyAsync(P.base + P.plane_stride, img_first_dx[s], bytes, cudaMemcpyHostToDevice, e->stream));
-    CU(cudaMemcpyAsync(P.base + 2 * P.plane_stride, img_first_dy[s], bytes, cudaMemcpyHostToDevice, e->stream));
+    if (e->stage.ensure(2 * bytes)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stage) failed");
+    float* st = e->stage.as<float>();   // planar dx, dy of the reference's API -> the engine's float2 plane
+    CU(cudaMemcpyAsync(st, img_first_dx[s], bytes, cudaMemcpyHostToDevice, e->stream));
+    CU(cudaMemcpyAsync(st + n, img_first_dy[s], bytes, cudaMemcpyHostToDevice, e->stream));
+    dis::launch_interleave(st, st + n, P.base + P.plane_stride, n, e->stream);
     CU(cudaMemcpyAsync(P.base + P.frame_stride, img_second[s], bytes, cudaMemcpyHostToDevice, e->stream));
   }
   e->launches = 0;
@@ -557,11 +577,16 @@ int dis_construct_pyramid(dis_engine* e, const float* img, int width, int height
     e->launches = dis::launch_pyramid(a, e->stream);
     CU(cudaGetLastError());
     for (int s = 0; s <= lv_f; ++s) {
-      const size_t bytes = sizeof(float) * (size_t)((width >> s) + 2 * img_padding) * ((height >> s) + 2 * img_padding);
+      const size_t n = (size_t)((width >> s) + 2 * img_padding) * ((height >> s) + 2 * img_padding), bytes = sizeof(float) * n;
       const dis::LevelPlanes& P = e->planes[s];
       if (img_pyr[s]) CU(cudaMemcpyAsync(img_pyr[s], P.base, bytes, cudaMemcpyDeviceToHost, e->stream));
-      if (img_dx_pyr[s]) CU(cudaMemcpyAsync(img_dx_pyr[s], P.base + P.plane_stride, bytes, cudaMemcpyDeviceToHost, e->stream));
-      if (img_dy_pyr[s]) CU(cudaMemcpyAsync(img_dy_pyr[s], P.base + 2 * P.plane_stride, bytes, cudaMemcpyDeviceToHost, e->stream));
+      if (img_dx_pyr[s] || img_dy_pyr[s]) {
+        if (e->stage.ensure(2 * bytes)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stage) failed");
+        float* st = e->stage.as<float>();
+        dis::launch_deinterleave(P.base + P.plane_stride, st, st + n, n, e->stream);
+        if (img_dx_pyr[s]) CU(cudaMemcpyAsync(img_dx_pyr[s], st, bytes, cudaMemcpyDeviceToHost, e->stream));
+        if (img_dy_pyr[s]) CU(cudaMemcpyAsync(img_dy_pyr[s], st + n, bytes, cudaMemcpyDeviceToHost, e->stream));
+      }
     }
     CU(cudaStreamSynchronize(e->stream));
     return DIS_OK;
@@ -626,7 +651,14 @@ int dis_get_plane(dis_engine* e, int frame, int scale, int which, float* out) {
   const dis::LevelPlanes& P = e->planes[scale];
   const size_t n = (size_t)((e->W >> scale) + 2 * e->pad) * ((e->H >> scale) + 2 * e->pad);
   CU(cudaSetDevice(e->device));
-  CU(cudaMemcpyAsync(out, P.base + P.frame_stride * frame + P.plane_stride * which, sizeof(float) * n, cudaMemcpyDeviceToHost, e->stream));
+  const float* src = P.base + P.frame_stride * frame;
+  if (which > 0) {
+    if (e->stage.ensure(2 * sizeof(float) * n)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stage) failed");
+    float* st = e->stage.as<float>();
+    dis::launch_deinterleave(src + P.plane_stride, st, st + n, n, e->stream);
+    src = st + (which - 1) * n;
+  }
+  CU(cudaMemcpyAsync(out, src, sizeof(float) * n, cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
   return DIS_OK;
 }
@@ -652,7 +684,7 @@ struct dis_grid {
   int pad;
   float lb, ub_w, ub_h;
   size_t plane_elems;
-  DevBuf planes, flow_prev, init, u, dense, pair;
+  DevBuf planes, flow_prev, init, u, dense, pair, stage;
   std::vector<float> init_host;
   bool have_first = false, have_second = false, use_prev = false, use_override = false, searched = false;
   std::vector<float> u_host;
@@ -681,8 +713,9 @@ int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_g
   g->lb = -(float)ps / 2; g->ub_w = (float)(width + ps / 2 - 2); g->ub_h = (float)(height + ps / 2 - 2);
   g->plane_elems = ((size_t)I.tmp_w * I.tmp_h + 3) & ~(size_t)3;
   const int2 pr = make_int2(0, 1);
-  if (g->planes.ensure(sizeof(float) * 6 * g->plane_elems) || g->u.ensure(sizeof(float) * 2 * I.num_patches) ||
-      g->dense.ensure(sizeof(float) * 2 * (size_t)width * height) || g->pair.ensure(sizeof(int2)) ||
+  if (g->planes.ensure(sizeof(float) * 6 * g->plane_elems) || g->stage.ensure(sizeof(float) * 2 * g->plane_elems) ||
+      g->u.ensure(sizeof(float) * 2 * I.num_patches) ||
+      g->dense.ensure(sizeof(float) * 2 * (size_t)width * height) || g->pair.ensure(64) ||
       g->init.ensure(sizeof(float) * 2 * I.num_patches) ||
       g->flow_prev.ensure(sizeof(float) * 2 * (size_t)(width / 2 + 1) * (height / 2 + 1))) {
     dis_grid_destroy(g);
@@ -699,6 +732,7 @@ void dis_grid_destroy(dis_grid* g) {
   cudaSetDevice(g->e->device);
   cudaStreamSynchronize(g->e->stream);
   g->planes.release(); g->flow_prev.release(); g->init.release(); g->u.release(); g->dense.release(); g->pair.release();
+  g->stage.release();
   delete g;
 }
 
@@ -706,10 +740,12 @@ int dis_grid_init(dis_grid* g, const float* img_first, const float* dx, const fl
   (void)img_first;   // gathered by the reference but never used
   if (!g || !dx || !dy) return fail(DIS_ERR_PARAM, "null argument");
   CU(cudaSetDevice(g->e->device));
-  const size_t bytes = sizeof(float) * (size_t)g->info.tmp_w * g->info.tmp_h;
+  const size_t n = (size_t)g->info.tmp_w * g->info.tmp_h, bytes = sizeof(float) * n;
   float* base = g->planes.as<float>();
-  CU(cudaMemcpyAsync(base + g->plane_elems, dx, bytes, cudaMemcpyHostToDevice, g->e->stream));
-  CU(cudaMemcpyAsync(base + 2 * g->plane_elems, dy, bytes, cudaMemcpyHostToDevice, g->e->stream));
+  float* st = g->stage.as<float>();
+  CU(cudaMemcpyAsync(st, dx, bytes, cudaMemcpyHostToDevice, g->e->stream));
+  CU(cudaMemcpyAsync(st + n, dy, bytes, cudaMemcpyHostToDevice, g->e->stream));
+  dis::launch_interleave(st, st + n, base + g->plane_elems, n, g->e->stream);
   CU(cudaStreamSynchronize(g->e->stream));
   std::fill(g->init_host.begin(), g->init_host.end(), 0.f);   // src/patch_grid.cpp:80
   g->use_prev = g->use_override = false;
@@ -759,6 +795,7 @@ int dis_grid_inverse_search(dis_grid* g) {
   memset(&a, 0, sizeof a);
   a.planes.base = g->planes.as<float>(); a.planes.plane_stride = g->plane_elems; a.planes.frame_stride = 3 * g->plane_elems;
   a.pairs = g->pair.as<int2>();
+  a.work_counter = g->pair.as<int>() + 8;
   a.flow_prev = g->use_prev ? g->flow_prev.as<float>() : nullptr;
   a.init_override = g->use_override ? g->init.as<float>() : nullptr;
   a.u_out = g->u.as<float>();
@@ -767,8 +804,8 @@ int dis_grid_inverse_search(dis_grid* g) {
   a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
   a.warps_per_pair = (I.num_patches + 31) / 32;
   a.iterations = e->prm.max_iter; a.patnorm = e->prm.patch_norm ? 1 : 0;
-  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.outlier = (float)e->prm.patch_size / 2;
-  a.conv_eps = e->prm.conv_eps;
+  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.out2max = sq_threshold((float)e->prm.patch_size / 2);
+  a.conv_eps2 = e->prm.conv_eps * e->prm.conv_eps;
   if (dis::launch_inverse_search(a, e->prm.patch_size, e->stream) < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
   CU(cudaGetLastError());
   g->u_host.resize(2 * (size_t)I.num_patches);

@@ -11,9 +11,12 @@
 namespace dis {
 
 // Planes of one pyramid level for all frames of a run, in HBM:
-//   base + frame*frame_stride + which*plane_stride + y*tmp_w + x     (which: 0 image, 1 dx, 2 dy)
-// Each plane is the reference's padded plane (src/main.cpp:41-49): (h+2*pad) x (w+2*pad),
-// replicate border for the image, zero border for the gradients.
+//   image:     base + frame*frame_stride + y*tmp_w + x                          (fp32)
+//   gradients: base + frame*frame_stride + plane_stride + 2*(y*tmp_w + x) + {0: dx, 1: dy}
+// i.e. the reference's padded planes (src/main.cpp:41-49): (h+2*pad) x (w+2*pad), replicate border
+// for the image, zero border for the gradients — with dx and dy INTERLEAVED as float2 so that a
+// template element is one 8-byte load.  The planar layout of the reference's float** API exists only
+// at the C-ABI boundary (launch_interleave / launch_deinterleave).
 struct LevelPlanes {
   float* base;
   size_t frame_stride;   // floats
@@ -33,14 +36,16 @@ struct SearchArgs {
   unsigned long long* counters;  // [4]: patch_iterations, sampled_iterations, resets, start_oob (or nullptr)
   void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
   int* straggler_count;     // number of entries (device)
+  int* work_counter;        // next patch index of the launch (device; zeroed by the launcher)
   int straggler_cap;
   int n_pairs;
   int width, height, pad, tmp_w;
   int npw, nph, offw, offh, steps, np;
   int warps_per_pair;
   int iterations, patnorm;
-  float lb, ub_w, ub_h, outlier;
-  float conv_eps;           // 0 = off (reference behaviour)
+  float lb, ub_w, ub_h;
+  float out2max;            // largest fp32 s with sqrtf(s) <= outlierthresh: |start-pos| > thr <=> s > out2max
+  float conv_eps2;          // conv_eps^2; 0 = off (reference behaviour)
 };
 
 struct DensifyArgs {
@@ -65,6 +70,9 @@ struct PyramidArgs {
   LevelPlanes planes[16];
 };
 int launch_pyramid(const PyramidArgs& a, cudaStream_t s);
+// planar dx, dy (n floats each) <-> interleaved float2 plane
+int launch_interleave(const float* dx, const float* dy, float* gxy, size_t n, cudaStream_t s);
+int launch_deinterleave(const float* gxy, float* dx, float* dy, size_t n, cudaStream_t s);
 
 // crop the divisibility padding of the finest dense flow into the output layout
 int launch_crop(const float* dense, size_t dense_stride, int W, int H, int left, int top, float* out,

@@ -91,22 +91,47 @@ __global__ void __launch_bounds__(256) k_sobel_border(const PyramidArgs A, int l
   if (X >= tw || Y >= th) return;
   const LevelPlanes& P = A.planes[lvl];
   float* img = P.base + (size_t)f * P.frame_stride;
-  float* gx = img + P.plane_stride;
-  float* gy = gx + P.plane_stride;
+  float2* gxy = reinterpret_cast<float2*>(img + P.plane_stride);
   const int x = X - pad, y = Y - pad;
   const size_t o = (size_t)Y * tw + X;
   if (x >= 0 && x < w && y >= 0 && y < h) {
     auto at = [&](int xx, int yy) { return img[(size_t)(yy + pad) * tw + (xx + pad)]; };
     const Sobel s = sobel_at(at, x, y, w, h);
-    gx[o] = s.gx; gy[o] = s.gy;
+    gxy[o] = make_float2(s.gx, s.gy);
   } else {
     const int cx = min(max(x, 0), w - 1), cy = min(max(y, 0), h - 1);
     img[o] = img[(size_t)(cy + pad) * tw + (cx + pad)];
-    gx[o] = 0.f; gy[o] = 0.f;
+    gxy[o] = make_float2(0.f, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_interleave(const float* __restrict__ dx, const float* __restrict__ dy,
+                                                    float2* __restrict__ gxy, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    gxy[i] = make_float2(dx[i], dy[i]);
+}
+
+__global__ void __launch_bounds__(256) k_deinterleave(const float2* __restrict__ gxy, float* __restrict__ dx,
+                                                      float* __restrict__ dy, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float2 v = gxy[i];
+    dx[i] = v.x; dy[i] = v.y;
   }
 }
 
 }  // namespace
+
+int launch_interleave(const float* dx, const float* dy, float* gxy, size_t n, cudaStream_t s) {
+  const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  k_interleave<<<blocks, 256, 0, s>>>(dx, dy, reinterpret_cast<float2*>(gxy), n);
+  return 1;
+}
+
+int launch_deinterleave(const float* gxy, float* dx, float* dy, size_t n, cudaStream_t s) {
+  const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  k_deinterleave<<<blocks, 256, 0, s>>>(reinterpret_cast<const float2*>(gxy), dx, dy, n);
+  return 1;
+}
 
 int launch_pyramid(const PyramidArgs& a, cudaStream_t s) {
   int n = 0;

@@ -8,23 +8,35 @@
 //   Patch::get_patch_second_image src/patch.cpp:207-267      4-tap resample + mean normalisation
 //
 // Design (B200-first, not a translation):
-//  * One LANE per patch carries the scalar state (u, pos, LU factors).  A block is a TILE of the
-//    patch grid: warp w owns grid column (8*tile_x + w), lanes are 32 consecutive grid rows, so the
-//    block's taps and templates share L1 lines.
-//  * The expensive part of a pass (ps^2 4-tap samples + three tree reductions) is done by an
-//    8-lane sub-warp per patch, four patches per warp round.  Lane j of a sub-warp owns the
-//    elements e == j (mod 8), which makes Eigen's SSE reduction tree (App. A.3) exactly
-//    "serial over the lane's elements, then xor-shuffle 4, 2, 1".
+//  * PERSISTENT warps, one LANE per patch ("walker").  A lane carries the scalar state of its patch
+//    (u, pos, LU factors); when the patch finishes the lane is re-bound to the next patch index of a
+//    global counter, so a warp never idles behind its slowest patch and the patches of a warp are
+//    at mixed phases (which keeps the service rounds below full).
+//  * The expensive part of a pass (ps^2 4-tap samples + three tree reductions) is done by a
+//    sub-group of SG lanes per patch (SG = 4 for ps <= 8, else 8), 32/SG patches per warp round.
+//    Lane j of a sub-group owns the elements e with e mod 8 in {j, j+4} (SG 4) or {j} (SG 8), which
+//    makes Eigen's SSE reduction tree (App. A.3) exactly "serial over the lane's elements, then
+//    [in-lane add | xor-shuffle 4], xor-shuffle 2, 1".
 //  * EXACT memoisation: within a patch, delta_u is a pure function of the bit pattern of the
 //    sampling position (H, the template and the image are constant), and so is the outcome of the
-//    reset test.  Each patch keeps a 16-entry, 4-way cache {pos bits -> delta_u} in shared memory;
-//    a pass whose position is cached costs a handful of scalar instructions instead of ~900.  The
-//    fp32 orbit of a patch revisits a few dozen positions (it jitters at the ulp of the
-//    coordinate), so ~98 % of the reference's 1001 passes per patch hit.  Results are bit-identical
-//    to running every pass: nothing is approximated, only recomputation is skipped.
-//  * Lanes that miss wait; the warp services misses in rounds of four so sub-warps stay busy.
-//  * Patches whose orbit never settles (~0.15 %) would keep one lane of a warp busy for ~1000
-//    rounds; they are handed to k_stragglers, which packs four of them per warp.
+//    reset test.  Each patch keeps a 16-entry cache {pos bits -> delta_u} in shared memory, 4 sets
+//    (low bit of x, low bit of y) x 4 ways, one uint4 {bx, by, dx, dy} per entry.  A pass whose
+//    position is cached costs ~15 scalar instructions instead of ~1000.  The fp32 orbit of a patch
+//    revisits a few positions (it jitters at the ulp of the coordinate), so ~98 % of the
+//    reference's 1001 passes per patch hit.  Results are bit-identical to running every pass:
+//    nothing is approximated, only recomputation is skipped.
+//  * Way prediction: an entry is inserted at the way named by bit 1 of x and y, so the hot loop
+//    probes ONE slot (a single LDS.128); the other three ways of the set are probed once per chunk
+//    of kChunk passes, for the lanes that fell out of the fast loop.
+//  * Lanes that miss (and freshly bound lanes, which need their template's Hessian) wait; at the end
+//    of each chunk the warp serves them in rounds (one patch per sub-group).  Sub-groups leave their
+//    sums in shared memory; the owners then run the reset test / LU solve / cache insert once, in
+//    parallel.
+//  * Patches whose orbit never settles (~0.6 %) sample on every pass; after kStreakLimit such passes
+//    they are handed to k_stragglers, which packs 32/SG of them per warp with the template in
+//    registers.
+//  (tools/micro/ keeps the measured alternatives: tile-bound warps, and warp-specialised
+//  walker/sampler blocks with a shared-memory request queue; DESIGN.md has the numbers.)
 #include <stdlib.h>
 
 #include "dis_kernels.cuh"
@@ -32,28 +44,48 @@
 namespace dis {
 namespace {
 
-constexpr int kWarpsPerBlock = 8;     // = grid columns per tile
-constexpr int kCacheEntries = 16;
-constexpr int kWays = 4;
+constexpr int kSlots = 16;            // cache entries per patch
+constexpr int kChunk = 8;             // fast-probe passes between two warp-level decisions
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kLonelyLimit = 8;       // consecutive under-filled forced rounds before a hand-off
 constexpr int kHandoffMinIter = 48;   // never hand off a patch that is still in its convergence phase
-constexpr int kCacheBytesPerWarp = kCacheEntries * 32 * 16;
 
-template <int PS>
+template <int PS, int SG>
 struct Geom {
   static constexpr int NE = PS * PS;
-  static constexpr int K = NE / 8;
-  static constexpr bool EXTRA = (NE % 8) >= 4;
-  static constexpr int KX = K + (EXTRA ? 1 : 0);
+  static constexpr int K = NE / 8;                       // full rounds of 8 (two SSE packets)
+  static constexpr bool EXTRA = (NE % 8) >= 4;           // one more packet of 4
+  static constexpr int H = 8 / SG;                       // residues mod 8 owned by a lane (1 or 2)
+  static constexpr int NPL = K * H + (EXTRA ? 1 : 0);    // elements per lane
+  static constexpr int G = 32 / SG;                      // patches per warp round
+  static constexpr bool POW2 = (NE & (NE - 1)) == 0;
 };
 
-// Eigen-3.3 redux of the per-lane partial sums.  `acc` is the lane's serial
-// sum over its elements c, c+8, ...; `extra` the element 8*floor(n/8) + (lane&3) when n%8 >= 4.
-template <bool EXTRA>
-__device__ __forceinline__ float tree_finish(float acc, float extra) {
-  acc = acc + __shfl_xor_sync(kFull, acc, 4);
-  if (EXTRA) acc = acc + extra;
+// Element index of the lane's i-th element (sl = lane within the sub-group).
+template <int PS, int SG>
+__device__ __forceinline__ int element_of(int i, int sl) {
+  using G = Geom<PS, SG>;
+  if (i < G::K) return 8 * i + sl;
+  if (SG == 4 && i < 2 * G::K) return 8 * (i - G::K) + sl + 4;
+  return 8 * G::K + (sl & 3);
+}
+
+// Eigen-3.3 redux of the sub-group's ps^2 values, v = the lane's elements in
+// element_of order.  Returns the sum in every lane of the sub-group.
+template <int PS, int SG>
+__device__ __forceinline__ float tree_sum(const float (&v)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
+  float acc = v[0];
+#pragma unroll
+  for (int i = 1; i < G::K; ++i) acc += v[i];
+  if (SG == 4) {
+    float hi = v[G::K];
+#pragma unroll
+    for (int i = 1; i < G::K; ++i) hi += v[G::K + i];
+    acc = acc + hi;                                      // packet 0 + packet 1
+  } else {
+    acc = acc + __shfl_xor_sync(kFull, acc, 4);
+  }
+  if (G::EXTRA) acc = acc + v[G::NPL - 1];
   acc = acc + __shfl_xor_sync(kFull, acc, 2);
   acc = acc + __shfl_xor_sync(kFull, acc, 1);
   return acc;
@@ -88,28 +120,57 @@ __device__ __forceinline__ void fix_singular(float& h00, float h01, float& h11) 
   }
 }
 
-// Element offsets of sub-lane `sl` inside a patch window, relative to the patch centre.
-template <int PS>
-__device__ __forceinline__ void element_offsets(int sl, int tw, int (&eoff)[Geom<PS>::KX]) {
-  using G = Geom<PS>;
+// Offsets (in pixels of a padded plane of width tw) of the lane's elements relative to the patch
+// centre; kept in registers for patch sizes other than 8 (ps 8 uses its column structure instead).
+template <int PS, int SG>
+__device__ __forceinline__ void element_offsets(int sl, int tw, int (&eoff)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
 #pragma unroll
-  for (int k = 0; k < G::KX; ++k) {
-    const int idx = (k < G::K) ? (sl + 8 * k) : (8 * G::K + (sl & 3));
+  for (int i = 0; i < G::NPL; ++i) {
+    const int idx = element_of<PS, SG>(i, sl);
     const int row = idx / PS, col = idx - row * PS;
-    eoff[k] = (row - PS / 2) * tw + (col - PS / 2);
+    eoff[i] = (row - PS / 2) * tw + (col - PS / 2);
   }
 }
 
-// Patch::get_patch_second_image (src/patch.cpp:207-267) for the sub-lane's elements, followed by
-// the two products-and-sums of src/patch.cpp:171-172.  gxv/gyv: the lane's template gradients.
-// Returns (sum gx*r, sum gy*r), identical in all 8 lanes of the sub-warp.
-template <int PS>
+// The lane's template gradients (gx, gy interleaved) of the patch centred at plane offset c
+// (Patch::get_gradients_on_patch, src/patch.cpp:47-73; the intensity template is never used, F2).
+template <int PS, int SG>
+__device__ __forceinline__ void load_template(const float2* __restrict__ gxy, int c, int tw, int sl,
+                                              const int (&eoff)[Geom<PS, SG>::NPL],
+                                              float2 (&T)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
+  if (PS == 8) {
+    const float2* col = gxy + c + (sl - 4) - 4 * tw;
+#pragma unroll
+    for (int h = 0; h < G::H; ++h)
+#pragma unroll
+      for (int r = 0; r < 8; ++r) T[8 * h + r] = __ldg(col + 4 * h + r * tw);
+  } else {
+#pragma unroll
+    for (int i = 0; i < G::NPL; ++i) T[i] = __ldg(gxy + c + eoff[i]);
+  }
+}
+
+// compute_hessian_matrix (src/patch.cpp:75-91): the three products-and-sums, in every lane.
+template <int PS, int SG>
+__device__ __forceinline__ float3 hessian_sums(const float2 (&T)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
+  float a[G::NPL], b[G::NPL], c[G::NPL];
+#pragma unroll
+  for (int i = 0; i < G::NPL; ++i) { a[i] = T[i].x * T[i].x; b[i] = T[i].x * T[i].y; c[i] = T[i].y * T[i].y; }
+  return make_float3(tree_sum<PS, SG>(a), tree_sum<PS, SG>(b), tree_sum<PS, SG>(c));
+}
+
+// Patch::get_patch_second_image (src/patch.cpp:207-267) for the lane's elements, followed by
+// the two products-and-sums of src/patch.cpp:171-172.  T: the lane's template gradients.
+// Returns (sum gx*r, sum gy*r), identical in all lanes of the sub-group.
+template <int PS, int SG>
 __device__ __forceinline__ float2 sample_and_project(const float* __restrict__ imB, int tw, int pad, int wmax,
                                                      int hmax, float opx, float opy, int sl, int patnorm,
-                                                     const int (&eoff)[Geom<PS>::KX],
-                                                     const float (&gxv)[Geom<PS>::KX],
-                                                     const float (&gyv)[Geom<PS>::KX]) {
-  using G = Geom<PS>;
+                                                     const int (&eoff)[Geom<PS, SG>::NPL],
+                                                     const float2 (&T)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
   const float fl = floorf(opx), fk = floorf(opy);
   const float a = opx - fl, b = opy - fk;
   const float w0 = (1 - a) * (1 - b), w1 = a * (1 - b), w2 = b * (1 - a), w3 = a * b;
@@ -120,317 +181,331 @@ __device__ __forceinline__ float2 sample_and_project(const float* __restrict__ i
   bxi = min(max(bxi, PS / 2 + 1), wmax);
   byi = min(max(byi, PS / 2 + 1), hmax);
   const float* __restrict__ ib = imB + byi * tw + bxi;
-  float v[G::KX];
+  float v[G::NPL];
   if (PS == 8) {
-    // lane sl owns column sl: rows share taps, 9 x 2 loads instead of 8 x 4
-    const float* col = ib + (sl - 4) - 5 * tw;
-    float t0[9], t1[9];
+    // the lane owns whole columns: consecutive rows share taps, 9 x 2 loads per column instead of 8 x 4
 #pragma unroll
-    for (int r = 0; r < 9; ++r) { t0[r] = __ldg(col + r * tw - 1); t1[r] = __ldg(col + r * tw); }
+    for (int h = 0; h < G::H; ++h) {
+      const float* col = ib + (sl + 4 * h - 4) - 5 * tw;
+      float t0[9], t1[9];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) v[r] = ((w3 * t1[r + 1] + w2 * t0[r + 1]) + w1 * t1[r]) + w0 * t0[r];
+      for (int r = 0; r < 9; ++r) { t0[r] = __ldg(col + r * tw - 1); t1[r] = __ldg(col + r * tw); }
+#pragma unroll
+      for (int r = 0; r < 8; ++r) v[8 * h + r] = ((w3 * t1[r + 1] + w2 * t0[r + 1]) + w1 * t1[r]) + w0 * t0[r];
+    }
   } else {
 #pragma unroll
-    for (int q = 0; q < G::KX; ++q) {
-      const float* t = ib + eoff[q];
-      v[q] = ((w3 * __ldg(t) + w2 * __ldg(t - 1)) + w1 * __ldg(t - tw)) + w0 * __ldg(t - tw - 1);
+    for (int i = 0; i < G::NPL; ++i) {
+      const float* t = ib + eoff[i];
+      v[i] = ((w3 * __ldg(t) + w2 * __ldg(t - 1)) + w1 * __ldg(t - tw)) + w0 * __ldg(t - tw - 1);
     }
   }
-  if (patnorm) {   // src/patch.cpp:264-266
-    float acc = v[0];
+  if (patnorm) {   // src/patch.cpp:264-266; x / 2^n == x * 2^-n bit for bit
+    const float sum = tree_sum<PS, SG>(v);
+    const float mean = G::POW2 ? sum * (1.0f / (float)G::NE) : sum / (float)G::NE;
 #pragma unroll
-    for (int q = 1; q < G::K; ++q) acc += v[q];
-    const float sum = tree_finish<G::EXTRA>(acc, G::EXTRA ? v[G::KX - 1] : 0.f);
-    const float mean = sum / (float)G::NE;
-#pragma unroll
-    for (int q = 0; q < G::KX; ++q) v[q] -= mean;
+    for (int i = 0; i < G::NPL; ++i) v[i] -= mean;
   }
-  float sgx = 0.f, sgy = 0.f, egx = 0.f, egy = 0.f;
+  float px[G::NPL], py[G::NPL];
 #pragma unroll
-  for (int q = 0; q < G::KX; ++q) {
-    const float tx = gxv[q] * v[q], ty = gyv[q] * v[q];
-    if (q == 0) { sgx = tx; sgy = ty; }
-    else if (q < G::K) { sgx += tx; sgy += ty; }
-    else { egx = tx; egy = ty; }
-  }
-  sgx = tree_finish<G::EXTRA>(sgx, egx);
-  sgy = tree_finish<G::EXTRA>(sgy, egy);
-  return make_float2(sgx, sgy);
+  for (int i = 0; i < G::NPL; ++i) { px[i] = T[i].x * v[i]; py[i] = T[i].y * v[i]; }
+  return make_float2(tree_sum<PS, SG>(px), tree_sum<PS, SG>(py));
 }
 
 // The reset test of src/patch.cpp:185-194 (plus NaN => reset).
+// sqrtf is correctly rounded and monotone, so  sqrtf(s) > outlier  <=>  s > out2max  where out2max
+// is the largest float whose root does not exceed outlier (found on the host, dis_api.cu).
 __device__ __forceinline__ bool must_reset(float px, float py, float stx, float sty, const SearchArgs& A) {
   const float ddx = stx - px, ddy = sty - py;
-  return sqrtf(ddx * ddx + ddy * ddy) > A.outlier || px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h ||
-         px != px || py != py;
+  const float s = ddx * ddx + ddy * ddy;
+  return !(s <= A.out2max) || px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py;
 }
 
-enum : int { ST_RUN = 0, ST_WAIT = 1, ST_DONE = 2 };
+enum : int { ST_RUN = 0, ST_WAIT = 1, ST_HESS = 2, ST_FREE = 3 };
 
-template <int PS, bool FAST>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+constexpr int kWarps = 8;            // warps per block (independent of one another)
+constexpr int kBlocksPerSM = 2;      // 16 warps per SM at <= 128 registers: a third block would spill into the hot loops
+constexpr int kStreakLimit = 64;     // consecutive first-seen positions before a patch is handed off
+constexpr int kRebindMin = 4;        // free lanes a warp gathers before it fetches new patches
+
+// per-warp shared memory
+struct WarpSmem {
+  uint4 cache[kSlots][32];           // per lane: 16 x {bx, by, dx, dy}
+  float4 res[32];                    // service results, per lane
+  int list[32];                      // lanes to serve, in rank order
+};
+
+// Geometry of patch `idx` of the launch (idx = pair * np + id; id = x*nph + y, src/patch_grid.cpp:39-49).
+struct PatchGeom { int pair, pid, rx, ry; };
+__device__ __forceinline__ PatchGeom patch_geom(const SearchArgs& A, int idx) {
+  PatchGeom g;
+  g.pair = idx / A.np;
+  g.pid = idx - g.pair * A.np;
+  const int gx = g.pid / A.nph, gy = g.pid - gx * A.nph;
+  g.rx = gx * A.steps + A.offw;
+  g.ry = gy * A.steps + A.offh;
+  return g;
+}
+
+template <int PS, int SG, bool FAST>
+__global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
 k_inverse_search(const SearchArgs A) {
-  using G = Geom<PS>;
+  using G = Geom<PS, SG>;
   extern __shared__ uint4 smem_raw[];
   const int lane = threadIdx.x & 31;
-  const int warp_in_block = threadIdx.x >> 5;
-  // tile decomposition: blockIdx.x -> (pair, tile_x, tile_y); warp = grid column inside the tile
-  const int tiles_x = (A.npw + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  const int tiles_y = (A.nph + 31) / 32;
-  const int tiles = tiles_x * tiles_y;
-  const int pair = blockIdx.x / tiles;
-  const int t = blockIdx.x - pair * tiles;
-  const int tile_x = t / tiles_y, tile_y = t - tile_x * tiles_y;
-  const int gx_i = tile_x * kWarpsPerBlock + warp_in_block;
-  if (gx_i >= A.npw) return;
-  const int gy_raw = tile_y * 32 + lane;
-  const bool valid = gy_raw < A.nph;
-  const int gy_i = valid ? gy_raw : A.nph - 1;
-  const int pid = gx_i * A.nph + gy_i;           // src/patch_grid.cpp:39-49: id = x*nph + y
-
-  // per-warp cache: keys x [4 sets][32 lanes] uint4 (4 ways), keys y likewise, deltas [16][32] float2
-  uint4* ckx = smem_raw + (size_t)warp_in_block * (kCacheBytesPerWarp / 16);
-  uint4* cky = ckx + 4 * 32;
-  float2* cdel = reinterpret_cast<float2*>(cky + 4 * 32);
-#pragma unroll
-  for (int s = 0; s < 4; ++s) {
-    ckx[s * 32 + lane] = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);   // NaN: never a key
-    cky[s * 32 + lane] = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-  }
-
-  const int2 fr = A.pairs[pair];
-  const float* __restrict__ gxA = A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride;
-  const float* __restrict__ gyA = gxA + A.planes.plane_stride;
-  const float* __restrict__ imB = A.planes.base + (size_t)fr.y * A.planes.frame_stride;
+  WarpSmem& W = reinterpret_cast<WarpSmem*>(smem_raw)[threadIdx.x >> 5];
+  uint4* cache = &W.cache[0][lane];                           // slot s at cache[s * 32]
   const int tw = A.tmp_w;
+  const int total = A.n_pairs * A.np;
   const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
+  const int sub = lane / SG, sl = lane % SG;
+  int eoff[G::NPL];
+  element_offsets<PS, SG>(sl, tw, eoff);
+  const int iters = A.iterations;
 
-  const int rx = gx_i * A.steps + A.offw, ry = gy_i * A.steps + A.offh;
-  const float refx = (float)rx, refy = (float)ry;
-  const int sub = lane >> 3, sl = lane & 7;
-  int eoff[G::KX];
-  element_offsets<PS>(sl, tw, eoff);
-
-  // ---- template gradients and Hessian (src/patch.cpp:47-91), 4 patches per round ----------------
-  float h00 = 0.f, h01 = 0.f, h11 = 0.f;
-#pragma unroll 1
-  for (int r = 0; r < 8; ++r) {
-    const int ory = __shfl_sync(kFull, ry, r * 4 + sub);
-    const int c = (ory + A.pad) * tw + (rx + A.pad);
-    float sxx = 0.f, sxy = 0.f, syy = 0.f, exx = 0.f, exy = 0.f, eyy = 0.f;
-#pragma unroll
-    for (int k = 0; k < G::KX; ++k) {
-      const float gx = __ldg(gxA + c + eoff[k]), gy = __ldg(gyA + c + eoff[k]);
-      const float pxx = gx * gx, pxy = gx * gy, pyy = gy * gy;
-      if (k == 0) { sxx = pxx; sxy = pxy; syy = pyy; }
-      else if (k < G::K) { sxx += pxx; sxy += pxy; syy += pyy; }
-      else { exx = pxx; exy = pxy; eyy = pyy; }
-    }
-    sxx = tree_finish<G::EXTRA>(sxx, exx);
-    sxy = tree_finish<G::EXTRA>(sxy, exy);
-    syy = tree_finish<G::EXTRA>(syy, eyy);
-    const float t00 = __shfl_sync(kFull, sxx, (lane & 3) * 8);
-    const float t01 = __shfl_sync(kFull, sxy, (lane & 3) * 8);
-    const float t11 = __shfl_sync(kFull, syy, (lane & 3) * 8);
-    if ((lane >> 2) == r) { h00 = t00; h01 = t01; h11 = t11; }
-  }
-  fix_singular(h00, h01, h11);
+  // per-lane patch state (a lane is re-bound to a new patch whenever it finishes one)
+  int state = ST_FREE, idx = -1, k = 0, pair = 0, coff = 0;
+  float refx = 0.f, refy = 0.f, inx = 0.f, iny = 0.f, stx = 0.f, sty = 0.f;
+  float ux = 0.f, uy = 0.f, px = 0.f, py = 0.f;
+  unsigned fifo = 0;
+  int streak = 0, k_posted = -2, waited = 0;
+  bool was_reset = false;
   LU2 lu;
-  lu.factor(h00, h01, h11);
+  lu.p = lu.q = lu.l = lu.u11 = 0.f; lu.swap = false;
+  unsigned long long c_iters = 0;
+  unsigned c_sampled = 0, c_resets = 0, c_oob = 0;
+  bool exhausted = false;
 
-  // ---- initial displacement (src/patch_grid.cpp:108-119) ----------------------------------------
-  float inx = 0.f, iny = 0.f;
-  if (A.init_override) {
-    const float2 v = reinterpret_cast<const float2*>(A.init_override)[(size_t)pair * A.np + pid];
-    inx = v.x; iny = v.y;
-  } else if (A.flow_prev) {
-    const int fx = (int)floorf(refx / 2), fy = (int)floorf(refy / 2);
-    const float2 v = reinterpret_cast<const float2*>(A.flow_prev + (size_t)pair * A.flow_prev_stride)[fy * (A.width / 2) + fx];
-    inx = v.x * 2; iny = v.y * 2;
-  }
-
-  // ---- Patch::inverse_search_start (src/patch.cpp:119-154) --------------------------------------
-  float ux = inx, uy = iny;
-  float px = refx + ux, py = refy + uy;
-  const float stx = px, sty = py;
-  int k = 0;                       // counter_iter
-  int state = ST_RUN;
-  unsigned fifo = 0;               // 2-bit round-robin pointer per set
-  unsigned n_sampled = 0, was_reset = 0, oob = 0;
-  if (!valid) state = ST_DONE;
-  else if (px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py) {
-    state = ST_DONE; oob = 1;
-  }
-
-  unsigned trip = 0;
-  int lonely = 0;
 #pragma unroll 1
   for (;;) {
-    // ---- scalar phase: consult the cache for the current position -----------------------------
-    {
-      const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-      const int set = ((bx & 1) << 1) | (by & 1);
-      const uint4 kx = ckx[set * 32 + lane], ky = cky[set * 32 + lane];
-      const bool m0 = (kx.x == bx) & (ky.x == by), m1 = (kx.y == bx) & (ky.y == by);
-      const bool m2 = (kx.z == bx) & (ky.z == by), m3 = (kx.w == bx) & (ky.w == by);
-      const bool hit = m0 | m1 | m2 | m3;
-      const int way = m1 ? 1 : m2 ? 2 : m3 ? 3 : 0;
-      const float2 d = cdel[((set << 2) + way) * 32 + lane];
-      const bool run = state == ST_RUN;
-      const bool over = k > A.iterations;                 // src/patch.cpp:199-201
-      if (run & hit & !over) {
-        ++k;
-        ux = ux - d.x; uy = uy - d.y;                     // src/patch.cpp:179
-        px = refx + ux; py = refy + uy;                   // src/patch.cpp:182
-        if (FAST) { if (sqrtf(d.x * d.x + d.y * d.y) < A.conv_eps) state = ST_DONE; }
-      } else if (run) {
-        state = hit ? ST_DONE : ST_WAIT;   // a first-seen position still owes its reset test (service round)
-      }
-    }
-    unsigned wait_mask = __ballot_sync(kFull, state == ST_WAIT);
-    const unsigned run_mask = __ballot_sync(kFull, state == ST_RUN);
-    if ((wait_mask | run_mask) == 0) break;
-    ++trip;
-    const int nwait = __popc(wait_mask);
-    const bool force = (run_mask == 0) || ((trip & 7) == 0);
-    if (run_mask != 0) lonely = 0;
-    if (nwait == 0 || (nwait < 4 && !force)) continue;
-
-    // ---- hand-off: the warp is down to a few lanes that miss on every pass ------------------------
-    if (run_mask == 0 && nwait < 4) ++lonely;
-    if (lonely > kLonelyLimit && A.stragglers) {
-      if (state == ST_WAIT && k >= kHandoffMinIter) {
-        const bool r = must_reset(px, py, stx, sty, A);
-        if (r) { ux = inx; uy = iny; was_reset = 1; state = ST_DONE; }
-        else if (k > A.iterations) state = ST_DONE;
-        else {
-          const int slot = atomicAdd(A.straggler_count, 1);
-          if (slot < A.straggler_cap) {
-            Straggler s; s.pair = pair; s.pid = pid; s.k = k; s.ux = ux; s.uy = uy;
-            reinterpret_cast<Straggler*>(A.stragglers)[slot] = s;
-            state = ST_DONE;
-            k = -1;          // results and counters come from k_stragglers
-          } else atomicSub(A.straggler_count, 1);
+    // ---- free lanes fetch new patches (a few lanes at a time) --------------------------------------
+    const unsigned free_m = __ballot_sync(kFull, state == ST_FREE);
+    if (free_m != 0 && !exhausted &&
+        (__popc(free_m) >= kRebindMin || __ballot_sync(kFull, state == ST_RUN) == 0)) {
+      const int leader = __ffs(free_m) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(A.work_counter, __popc(free_m));
+      base = __shfl_sync(kFull, base, leader);
+      if (base + __popc(free_m) >= total) exhausted = true;
+      if (state == ST_FREE) {
+        idx = base + __popc(free_m & ((1u << lane) - 1u));
+        if (idx < total) {
+          const PatchGeom g = patch_geom(A, idx);
+          pair = g.pair;
+          coff = (g.ry + A.pad) * tw + (g.rx + A.pad);
+          refx = (float)g.rx; refy = (float)g.ry;
+          inx = 0.f; iny = 0.f;                              // src/patch_grid.cpp:108-119
+          if (A.init_override) {
+            const float2 v = reinterpret_cast<const float2*>(A.init_override)[idx];
+            inx = v.x; iny = v.y;
+          } else if (A.flow_prev) {
+            const int fx = (int)floorf(refx / 2), fy = (int)floorf(refy / 2);
+            const float2 v = reinterpret_cast<const float2*>(A.flow_prev + (size_t)g.pair * A.flow_prev_stride)[fy * (A.width / 2) + fx];
+            inx = v.x * 2; iny = v.y * 2;
+          }
+          ux = inx; uy = iny;                                // Patch::inverse_search_start, src/patch.cpp:119-154
+          px = refx + ux; py = refy + uy;
+          stx = px; sty = py;
+          k = 0; fifo = 0; streak = 0; k_posted = -2; was_reset = false; waited = 0;
+#pragma unroll
+          for (int s = 0; s < kSlots; ++s) cache[s * 32] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
+          if (px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py) {
+            ++c_oob;                                         // start out of bounds: u = init, 0 passes
+            reinterpret_cast<float2*>(A.u_out)[idx] = make_float2(ux, uy);
+            if (A.iters_out) A.iters_out[idx] = 0;
+          } else state = ST_HESS;                            // first the template's Hessian (a service round)
         }
       }
-      wait_mask = __ballot_sync(kFull, state == ST_WAIT);
-      if (wait_mask == 0) continue;
     }
 
-    // ---- service rounds: four waiting patches at a time, one per 8-lane sub-warp ----------------
-#pragma unroll 1
-    while (wait_mask != 0 && (__popc(wait_mask) >= 4 || force)) {
-      unsigned m = wait_mask;
-      const int s0 = __ffs(m) - 1; m &= m - 1;
-      const int s1 = m ? __ffs(m) - 1 : s0; m &= m - 1;
-      const int s2 = m ? __ffs(m) - 1 : s0; m &= m - 1;
-      const int s3 = m ? __ffs(m) - 1 : s0; m &= m - 1;
-      wait_mask = m;
-      const int src = sub == 0 ? s0 : sub == 1 ? s1 : sub == 2 ? s2 : s3;
-      const float opx = __shfl_sync(kFull, px, src), opy = __shfl_sync(kFull, py, src);
-      const int ory = __shfl_sync(kFull, ry, src);
-      const int c = (ory + A.pad) * tw + (rx + A.pad);
-      float gxv[G::KX], gyv[G::KX];
+    // ---- fast phase: kChunk passes probing only the predicted way; a lane leaves it at its first
+    //      miss (or when it is done) and idles until the chunk ends -----------------------------------
+    bool run = state == ST_RUN;
+    bool fin = false;                                        // the lane's patch is finished in this round
 #pragma unroll
-      for (int q = 0; q < G::KX; ++q) { gxv[q] = __ldg(gxA + c + eoff[q]); gyv[q] = __ldg(gyA + c + eoff[q]); }
-      const float2 sg = sample_and_project<PS>(imB, tw, A.pad, wmax, hmax, opx, opy, sl, A.patnorm, eoff, gxv, gyv);
+    for (int it = 0; it < kChunk; ++it) {
+      const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
+      const uint4 e = cache[(((bx & 3) << 2) | (by & 3)) * 32];
+      run = run && e.x == bx && e.y == by && k <= iters;
+      if (run) {
+        ++k;
+        const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
+        ux = ux - dx; uy = uy - dy;                         // src/patch.cpp:179
+        px = refx + ux; py = refy + uy;                     // src/patch.cpp:182
+        if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) { run = false; fin = true; } }
+      }
+    }
+    // ---- lanes that left the fast phase: probe all four ways of the set ---------------------------
+    if (state == ST_RUN && !run && !fin) {
+      const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
+      const int p = ((bx & 3) << 2) | (by & 3);
+      const uint4 e0 = cache[p * 32], e1 = cache[(p ^ 8) * 32], e2 = cache[(p ^ 2) * 32], e3 = cache[(p ^ 10) * 32];
+      const bool m0 = e0.x == bx && e0.y == by, m1 = e1.x == bx && e1.y == by;
+      const bool m2 = e2.x == bx && e2.y == by, m3 = e3.x == bx && e3.y == by;
+      if (m0 || m1 || m2 || m3) {
+        if (k > iters) fin = true;                          // src/patch.cpp:199-201 (position already vetted)
+        else {
+          const uint4 e = m0 ? e0 : m1 ? e1 : m2 ? e2 : e3;
+          ++k;
+          const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
+          ux = ux - dx; uy = uy - dy;
+          px = refx + ux; py = refy + uy;
+          if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) fin = true; }
+        }
+      } else {
+        // a first-seen position: it owes its reset test and a sample
+        streak = (k == k_posted + 1) ? streak + 1 : 1;
+        k_posted = k;
+        state = ST_WAIT;
+        if (streak >= kStreakLimit && k >= kHandoffMinIter && A.stragglers) {
+          // the orbit does not settle: hand the patch to k_stragglers
+          if (must_reset(px, py, stx, sty, A)) { ux = inx; uy = iny; was_reset = true; fin = true; }
+          else if (k > iters) fin = true;
+          else {
+            const int slot = atomicAdd(A.straggler_count, 1);
+            if (slot < A.straggler_cap) {
+              Straggler s; s.pair = pair; s.pid = idx - pair * A.np; s.k = k; s.ux = ux; s.uy = uy;
+              reinterpret_cast<Straggler*>(A.stragglers)[slot] = s;
+              state = ST_FREE;     // results and counters come from k_stragglers
+            } else { atomicSub(A.straggler_count, 1); streak = 0; }
+          }
+        }
+      }
+    }
 
-      // hand the two sums to the owning lanes
-      const int slot = lane == s0 ? 0 : lane == s1 ? 1 : lane == s2 ? 2 : 3;
-      const float g0 = __shfl_sync(kFull, sg.x, slot * 8), g1 = __shfl_sync(kFull, sg.y, slot * 8);
-      const bool mine = (state == ST_WAIT) && (lane == s0 || lane == s1 || lane == s2 || lane == s3);
-      if (mine) {
-        if (must_reset(px, py, stx, sty, A)) {             // src/patch.cpp:185-194
-          ux = inx; uy = iny; was_reset = 1; state = ST_DONE;
-        } else if (k > A.iterations) {                     // src/patch.cpp:199-201
-          state = ST_DONE;
-        } else {
-          const float2 d = lu.solve(g0, g1);               // src/patch.cpp:176
-          const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-          const int set = ((bx & 1) << 1) | (by & 1);
+    // ---- service: waiting patches (first-seen positions, new templates), one per sub-group and round.
+    //      Whole rounds; an under-filled last round only if it is at least half full, nothing else can
+    //      run, or one of its patches has already waited a chunk. -------------------------------------
+    const bool needs = (state == ST_WAIT || state == ST_HESS) && !fin;
+    const unsigned wait_mask = __ballot_sync(kFull, needs);
+    bool served = false;
+    if (wait_mask != 0) {
+      const int nwait = __popc(wait_mask);
+      const int rem = nwait % G::G;
+      const bool others = __ballot_sync(kFull, state == ST_RUN && !fin) != 0;
+      const bool aged = __any_sync(kFull, needs && waited > 0);
+      const int nserv = (!others || 2 * rem >= G::G || aged) ? nwait : nwait - rem;
+      const int rank = __popc(wait_mask & ((1u << lane) - 1u));
+      served = needs && rank < nserv;
+      if (served) W.list[rank] = lane;
+      __syncwarp();
+#pragma unroll 1
+      for (int base = 0; base < nserv; base += G::G) {
+        const int src = W.list[min(base + sub, nserv - 1)];
+        const float opx = __shfl_sync(kFull, px, src), opy = __shfl_sync(kFull, py, src);
+        const int oc = __shfl_sync(kFull, coff, src), opair = __shfl_sync(kFull, pair, src);
+        const int kind = __shfl_sync(kFull, state, src) == ST_HESS;
+        const int2 fr = A.pairs[opair];
+        const float2* __restrict__ gxyA =
+            reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
+        const float* __restrict__ imB = A.planes.base + (size_t)fr.y * A.planes.frame_stride;
+        float2 T[G::NPL];
+        load_template<PS, SG>(gxyA, oc, tw, sl, eoff, T);
+        float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
+        const unsigned kinds = __ballot_sync(kFull, kind != 0);
+        if (kinds != 0) {                                    // compute_hessian_matrix, src/patch.cpp:75-91
+          const float3 hs = hessian_sums<PS, SG>(T);
+          if (kind) out = make_float4(hs.x, hs.y, hs.z, 0.f);
+        }
+        if (kinds != kFull) {
+          const float2 sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, opx, opy, sl, A.patnorm, eoff, T);
+          if (!kind) out = make_float4(sg.x, sg.y, 0.f, 0.f);
+        }
+        if (sl == 0) W.res[src] = out;
+      }
+      __syncwarp();
+    }
+    if (served) {
+      const float4 g = W.res[lane];
+      waited = 0;
+      if (state == ST_HESS) {
+        float h00 = g.x, h11 = g.z;
+        fix_singular(h00, g.y, h11);
+        lu.factor(h00, g.y, h11);
+        state = ST_RUN;
+      } else if (must_reset(px, py, stx, sty, A)) {          // src/patch.cpp:185-194
+        ux = inx; uy = iny; was_reset = true; fin = true;
+      } else if (k > iters) {                                // src/patch.cpp:199-201
+        fin = true;
+      } else {
+        const float2 d = lu.solve(g.x, g.y);                 // src/patch.cpp:176
+        const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
+        const int p = ((bx & 3) << 2) | (by & 3);
+        const uint4 old = cache[p * 32];
+        if (old.x != 0xffffffffu) {                           // predicted way taken: evict the set's FIFO victim
+          const int set = ((p >> 1) & 2) | (p & 1);
           const int way = (fifo >> (2 * set)) & 3;
           fifo = (fifo & ~(3u << (2 * set))) | (((way + 1) & 3) << (2 * set));
-          reinterpret_cast<unsigned*>(ckx)[(set * 32 + lane) * 4 + way] = bx;
-          reinterpret_cast<unsigned*>(cky)[(set * 32 + lane) * 4 + way] = by;
-          cdel[((set << 2) + way) * 32 + lane] = d;
-          ++n_sampled;
-          ++k;
-          ux = ux - d.x; uy = uy - d.y;
-          px = refx + ux; py = refy + uy;
-          state = ST_RUN;
-          if (FAST) { if (sqrtf(d.x * d.x + d.y * d.y) < A.conv_eps) state = ST_DONE; }
+          const int q = (p & 5) | ((way & 2) << 2) | ((way & 1) << 1);
+          if (q != p) cache[q * 32] = old;                    // the displaced entry moves there
         }
+        cache[p * 32] = make_uint4(bx, by, __float_as_uint(d.x), __float_as_uint(d.y));
+        ++c_sampled;
+        ++k;
+        ux = ux - d.x; uy = uy - d.y;
+        px = refx + ux; py = refy + uy;
+        state = ST_RUN;
+        if (FAST) { if (d.x * d.x + d.y * d.y < A.conv_eps2) fin = true; }
       }
+    } else if (needs) ++waited;
+    if (fin) {                                               // Patch::get_u_vector of a finished patch
+      reinterpret_cast<float2*>(A.u_out)[idx] = make_float2(ux, uy);
+      if (A.iters_out) A.iters_out[idx] = k;
+      c_iters += (unsigned long long)k;
+      c_resets += was_reset ? 1u : 0u;
+      state = ST_FREE;
     }
-  }
-
-  // ---- results ----------------------------------------------------------------------------------
-  const bool mine_out = valid && k >= 0;
-  if (mine_out) {
-    reinterpret_cast<float2*>(A.u_out)[(size_t)pair * A.np + pid] = make_float2(ux, uy);
-    if (A.iters_out) A.iters_out[(size_t)pair * A.np + pid] = k;
+    if (exhausted && __ballot_sync(kFull, state != ST_FREE) == 0) break;
   }
   if (A.counters) {
-    unsigned long long it = mine_out ? (unsigned long long)k : 0ull;
-    unsigned ns = valid ? n_sampled : 0u, nr = was_reset, no = oob;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-      it += __shfl_xor_sync(kFull, it, o);
-      ns += __shfl_xor_sync(kFull, ns, o);
-      nr += __shfl_xor_sync(kFull, nr, o);
-      no += __shfl_xor_sync(kFull, no, o);
+      c_iters += __shfl_xor_sync(kFull, c_iters, o);
+      c_sampled += __shfl_xor_sync(kFull, c_sampled, o);
+      c_resets += __shfl_xor_sync(kFull, c_resets, o);
+      c_oob += __shfl_xor_sync(kFull, c_oob, o);
     }
-    if (lane == 0) {
-      atomicAdd(&A.counters[0], it);
-      atomicAdd(&A.counters[1], (unsigned long long)ns);
-      atomicAdd(&A.counters[2], (unsigned long long)nr);
-      atomicAdd(&A.counters[3], (unsigned long long)no);
+    if (lane == 0 && (c_iters | c_sampled | c_resets | c_oob)) {
+      atomicAdd(&A.counters[0], c_iters);
+      atomicAdd(&A.counters[1], (unsigned long long)c_sampled);
+      atomicAdd(&A.counters[2], (unsigned long long)c_resets);
+      atomicAdd(&A.counters[3], (unsigned long long)c_oob);
     }
   }
 }
 
-// Patches handed off by k_inverse_search: every pass samples, four patches per warp (one per
-// 8-lane sub-warp, template gradients in registers).  Same arithmetic, same order of tests.
-template <int PS, bool FAST>
+// Patches handed off by k_inverse_search: every pass samples, one patch per sub-group with its
+// template gradients in registers.  Same arithmetic, same order of tests.
+template <int PS, int SG, bool FAST>
 __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
-  using G = Geom<PS>;
-  const int lane = threadIdx.x & 31, sub = lane >> 3, sl = lane & 7;
+  using G = Geom<PS, SG>;
+  const int lane = threadIdx.x & 31, sub = lane / SG, sl = lane % SG;
   const int gwarp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int nwarps = gridDim.x * (blockDim.x >> 5);
   const int count = min(*A.straggler_count, A.straggler_cap);
   const Straggler* list = reinterpret_cast<const Straggler*>(A.stragglers);
   const int tw = A.tmp_w;
   const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
-  int eoff[G::KX];
-  element_offsets<PS>(sl, tw, eoff);
+  int eoff[G::NPL];
+  element_offsets<PS, SG>(sl, tw, eoff);
   unsigned long long it_total = 0;
   unsigned ns_total = 0, nr_total = 0;
 #pragma unroll 1
-  for (int base = gwarp * 4; base < count; base += nwarps * 4) {
+  for (int base = gwarp * G::G; base < count; base += nwarps * G::G) {
     const bool have = base + sub < count;
     const Straggler e = list[have ? base + sub : base];
     const int2 fr = A.pairs[e.pair];
-    const float* __restrict__ gxA = A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride;
-    const float* __restrict__ gyA = gxA + A.planes.plane_stride;
+    const float2* __restrict__ gxyA =
+        reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
     const float* __restrict__ imB = A.planes.base + (size_t)fr.y * A.planes.frame_stride;
     const int gx_i = e.pid / A.nph, gy_i = e.pid - gx_i * A.nph;
     const int rx = gx_i * A.steps + A.offw, ry = gy_i * A.steps + A.offh;
     const float refx = (float)rx, refy = (float)ry;
-    const int c = (ry + A.pad) * tw + (rx + A.pad);
-    float gxv[G::KX], gyv[G::KX];
-    float sxx = 0.f, sxy = 0.f, syy = 0.f, exx = 0.f, exy = 0.f, eyy = 0.f;
-#pragma unroll
-    for (int k = 0; k < G::KX; ++k) {
-      const float gx = __ldg(gxA + c + eoff[k]), gy = __ldg(gyA + c + eoff[k]);
-      gxv[k] = gx; gyv[k] = gy;
-      const float pxx = gx * gx, pxy = gx * gy, pyy = gy * gy;
-      if (k == 0) { sxx = pxx; sxy = pxy; syy = pyy; }
-      else if (k < G::K) { sxx += pxx; sxy += pxy; syy += pyy; }
-      else { exx = pxx; exy = pxy; eyy = pyy; }
-    }
-    float h00 = tree_finish<G::EXTRA>(sxx, exx);
-    const float h01 = tree_finish<G::EXTRA>(sxy, exy);
-    float h11 = tree_finish<G::EXTRA>(syy, eyy);
+    float2 T[G::NPL];
+    load_template<PS, SG>(gxyA, (ry + A.pad) * tw + (rx + A.pad), tw, sl, eoff, T);
+    const float3 h = hessian_sums<PS, SG>(T);
+    float h00 = h.x, h11 = h.z;
+    const float h01 = h.y;
     fix_singular(h00, h01, h11);
     LU2 lu;
     lu.factor(h00, h01, h11);
@@ -451,7 +526,7 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
     unsigned was_reset = 0, ns = 0;
 #pragma unroll 1
     while (__any_sync(kFull, active)) {
-      const float2 sg = sample_and_project<PS>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, gxv, gyv);
+      const float2 sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
       if (active) {
         if (must_reset(px, py, stx, sty, A)) { ux = inx; uy = iny; was_reset = 1; active = false; }
         else if (k > A.iterations) active = false;
@@ -460,7 +535,7 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
           ++k; ++ns;
           ux = ux - d.x; uy = uy - d.y;
           px = refx + ux; py = refy + uy;
-          if (FAST) { if (sqrtf(d.x * d.x + d.y * d.y) < A.conv_eps) active = false; }
+          if (FAST) { if (d.x * d.x + d.y * d.y < A.conv_eps2) active = false; }
         }
       }
     }
@@ -485,28 +560,30 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
   }
 }
 
-template <int PS, bool FAST>
-int launch_ps(const SearchArgs& a, cudaStream_t s, int smem_pad) {
-  const size_t smem = (size_t)kWarpsPerBlock * kCacheBytesPerWarp + (size_t)smem_pad;
-  cudaFuncSetAttribute(k_inverse_search<PS, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  const int tiles_x = (a.npw + kWarpsPerBlock - 1) / kWarpsPerBlock, tiles_y = (a.nph + 31) / 32;
-  const unsigned blocks = (unsigned)(tiles_x * tiles_y) * (unsigned)a.n_pairs;
+template <int PS, int SG, bool FAST>
+int launch_ps(const SearchArgs& a, cudaStream_t s) {
+  const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
+  cudaFuncSetAttribute(k_inverse_search<PS, SG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(k_inverse_search<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  // persistent warps: lanes fetch patches from a global counter until the level is done
+  const long long total = (long long)a.n_pairs * a.np;
+  const long long want = (total + kWarps * 32 - 1) / (kWarps * 32);
+  const unsigned blocks = (unsigned)(want < 148 * kBlocksPerSM ? want : 148 * kBlocksPerSM);
   int n = 1;
+  cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) cudaMemsetAsync(a.straggler_count, 0, sizeof(int), s);
-  k_inverse_search<PS, FAST><<<blocks, kWarpsPerBlock * 32, smem, s>>>(a);
-  if (a.stragglers) { k_stragglers<PS, FAST><<<148 * 4, 128, 0, s>>>(a); ++n; }
+  k_inverse_search<PS, SG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
+  if (a.stragglers) { k_stragglers<PS, SG, FAST><<<148 * 4, 128, 0, s>>>(a); ++n; }
   return n;
 }
 
 }  // namespace
 
 int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s) {
-  static int smem_pad = -1;
-  if (smem_pad < 0) { const char* e = getenv("DIS_SMEM_PAD_KB"); smem_pad = e ? atoi(e) * 1024 : 0; }
-  const bool fast = a.conv_eps > 0.f;
-#define DIS_CASE(PS) case PS: return fast ? launch_ps<PS, true>(a, s, smem_pad) : launch_ps<PS, false>(a, s, smem_pad);
+  const bool fast = a.conv_eps2 > 0.f;
+#define DIS_CASE(PS, SG) case PS: return fast ? launch_ps<PS, SG, true>(a, s) : launch_ps<PS, SG, false>(a, s);
   switch (patch_size) {
-    DIS_CASE(4) DIS_CASE(6) DIS_CASE(8) DIS_CASE(10) DIS_CASE(12) DIS_CASE(16)
+    DIS_CASE(4, 4) DIS_CASE(6, 4) DIS_CASE(8, 4) DIS_CASE(10, 8) DIS_CASE(12, 8) DIS_CASE(16, 8)
     default: return -1;
   }
 #undef DIS_CASE
