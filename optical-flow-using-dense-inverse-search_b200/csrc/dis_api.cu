@@ -43,6 +43,8 @@ struct DevBuf {
   template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+constexpr int kMaxGroups = 4;
+
 struct Level {            // one entry per scale finest..coarsest, index s = scale - finest
   dis_level_info info;
   float lb, ub_w, ub_h;
@@ -58,8 +60,16 @@ struct dis_engine {
   int steps = 1;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  std::vector<cudaEvent_t> search_ev;   // pairs of events around each search launch
-  int search_launches = 0;
+  // Pairs are independent: a run is split into up to kMaxGroups groups of pairs, each with its own
+  // stream, so that the latency-bound tails of one group's level (few patches left, straggler chains)
+  // overlap with the bulk of another's.
+  std::vector<cudaStream_t> gstream;    // group streams (group 0 runs on `stream` itself)
+  std::vector<cudaEvent_t> gdone;
+  cudaEvent_t fork_ev = nullptr;
+  int n_groups = 1;                     // groups of the last run
+  std::vector<cudaEvent_t> search_ev;   // [group][level] pairs of events around each search launch
+  int search_launches = 0;              // per group
+  size_t straggler_stride = 0;          // bytes per group in `stragglers`
 
   // geometry of the current run
   int w0 = 0, h0 = 0, W = 0, H = 0, left = 0, top = 0, pad = 0;
@@ -67,6 +77,7 @@ struct dis_engine {
   bool have_run = false;
   bool stats_fetched = false;
   bool keep_iters = true;
+  int max_groups = 1;                   // DIS_GROUPS overrides; measured: no gain on B200 (levels are work-bound, not tail-bound)
 
   DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers, stage;
   int straggler_cap = 0;
@@ -166,7 +177,8 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
     size_t maxp = 0;
     for (const Level& L : e->levels) maxp = std::max(maxp, (size_t)L.info.num_patches * n_pairs);
     e->straggler_cap = (int)std::min<size_t>(maxp / 8 + 4096, (size_t)1 << 28);
-    if (e->stragglers.ensure(64 + (size_t)e->straggler_cap * 20)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stragglers) failed");
+    e->straggler_stride = (64 + (size_t)e->straggler_cap * 20 + 255) & ~(size_t)255;
+    if (e->stragglers.ensure(kMaxGroups * e->straggler_stride)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stragglers) failed");
   }
   return DIS_OK;
 }
@@ -175,34 +187,31 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
 
 namespace {
 
-// The coarse-to-fine loop of src/optical_flow.cpp:67-90 for all pairs of the run, on e->stream.
-int run_levels(dis_engine* e) {
+// The coarse-to-fine loop of src/optical_flow.cpp:67-90 for pairs [p0, p1) of the run on stream `st`.
+int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
   const dis_params& p = e->prm;
   const int nl = (int)e->levels.size();
-  CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
-  while ((int)e->search_ev.size() < 2 * nl) {
-    cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev);
-  }
-  e->search_launches = 0;
-  unsigned long long patches = 0;
-  for (int s = nl - 1; s >= 0; --s) {
+  char* sbase = e->stragglers.as<char>() + (size_t)g * e->straggler_stride;
+  int launch = 0;
+  for (int s = nl - 1; s >= 0; --s, ++launch) {
     Level& L = e->levels[s];
     const dis_level_info& I = L.info;
     dis::SearchArgs a;
     memset(&a, 0, sizeof a);
     a.planes = e->planes[I.scale];
-    a.pairs = e->pairs.as<int2>();
-    a.flow_prev = (s < nl - 1) ? e->levels[s + 1].flow.as<float>() : nullptr;
+    a.pairs = e->pairs.as<int2>() + p0;
+    a.flow_prev = (s < nl - 1) ? e->levels[s + 1].flow.as<float>() + e->levels[s + 1].flow_stride * p0 : nullptr;
     a.flow_prev_stride = (s < nl - 1) ? e->levels[s + 1].flow_stride : 0;
     a.init_override = nullptr;
-    a.u_out = L.u.as<float>();
-    a.iters_out = e->keep_iters ? L.iters.as<int>() : nullptr;
+    a.u_out = L.u.as<float>() + 2 * (size_t)I.num_patches * p0;
+    a.iters_out = e->keep_iters ? L.iters.as<int>() + (size_t)I.num_patches * p0 : nullptr;
     a.counters = e->counters.as<unsigned long long>();
-    a.straggler_count = e->stragglers.as<int>();
-    a.work_counter = e->stragglers.as<int>() + 8;
-    a.stragglers = e->stragglers.as<char>() + 64;
+    a.straggler_count = reinterpret_cast<int*>(sbase);
+    a.work_counter = reinterpret_cast<int*>(sbase) + 8;
+    a.stragglers = sbase + 64;
     a.straggler_cap = e->straggler_cap;
-    a.n_pairs = e->n_pairs;
+    a.n_pairs = p1 - p0;
+    a.share = e->n_groups;
     a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
     a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
     a.warps_per_pair = (I.num_patches + 31) / 32;
@@ -210,20 +219,49 @@ int run_levels(dis_engine* e) {
     a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
     a.out2max = sq_threshold((float)p.patch_size / 2);   // outlierthresh, src/optical_flow.cpp:34
     a.conv_eps2 = p.conv_eps * p.conv_eps;
-    CU(cudaEventRecord(e->search_ev[2 * e->search_launches], e->stream));
-    const int n = dis::launch_inverse_search(a, p.patch_size, e->stream);
+    cudaEvent_t* ev = &e->search_ev[2 * (g * nl + launch)];
+    CU(cudaEventRecord(ev[0], st));
+    const int n = dis::launch_inverse_search(a, p.patch_size, st);
     if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
-    CU(cudaEventRecord(e->search_ev[2 * e->search_launches + 1], e->stream));
-    e->search_launches++;
+    CU(cudaEventRecord(ev[1], st));
     e->launches += n;
     dis::DensifyArgs d;
-    d.u = L.u.as<float>(); d.dense = L.flow.as<float>(); d.dense_stride = L.flow_stride;
-    d.n_pairs = e->n_pairs; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
+    d.u = a.u_out; d.dense = L.flow.as<float>() + L.flow_stride * p0; d.dense_stride = L.flow_stride;
+    d.n_pairs = p1 - p0; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
     d.offw = I.offw; d.offh = I.offh; d.steps = I.steps; d.np = I.num_patches; d.ps = p.patch_size;
-    e->launches += dis::launch_densify(d, e->stream);
-    patches += (unsigned long long)I.num_patches * e->n_pairs;
+    e->launches += dis::launch_densify(d, st);
   }
+  return DIS_OK;
+}
+
+int run_levels(dis_engine* e) {
+  const int nl = (int)e->levels.size();
+  CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
+  const int G = std::max(1, std::min(std::min(kMaxGroups, e->max_groups), e->n_pairs));
+  while ((int)e->search_ev.size() < 2 * nl * G) {
+    cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev);
+  }
+  while ((int)e->gstream.size() < G - 1) {
+    cudaStream_t st; cudaEvent_t ev;
+    CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    e->gstream.push_back(st); e->gdone.push_back(ev);
+  }
+  if (!e->fork_ev) CU(cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming));
+  e->n_groups = G;
+  e->search_launches = nl;
+  if (G > 1) CU(cudaEventRecord(e->fork_ev, e->stream));
+  for (int g = G - 1; g >= 0; --g) {          // group 0 last: it runs on the engine's own stream
+    const int p0 = (int)((long long)e->n_pairs * g / G), p1 = (int)((long long)e->n_pairs * (g + 1) / G);
+    cudaStream_t st = g == 0 ? e->stream : e->gstream[g - 1];
+    if (g > 0) CU(cudaStreamWaitEvent(st, e->fork_ev, 0));
+    if (int rc = run_levels_group(e, g, p0, p1, st)) return rc;
+    if (g > 0) CU(cudaEventRecord(e->gdone[g - 1], st));
+  }
+  for (int g = 1; g < G; ++g) CU(cudaStreamWaitEvent(e->stream, e->gdone[g - 1], 0));
   CU(cudaGetLastError());
+  unsigned long long patches = 0;
+  for (const Level& L : e->levels) patches += (unsigned long long)L.info.num_patches * e->n_pairs;
   e->stats.patches = patches;
   e->have_run = true;
   e->stats_fetched = false;
@@ -312,6 +350,7 @@ int dis_create(const dis_params* p, int device, dis_engine** out) {
   dis_engine* e = new dis_engine();
   e->prm = *p; e->device = device;
   e->steps = steps_of(p->patch_size, p->patch_overlap);
+  if (const char* g = getenv("DIS_GROUPS")) e->max_groups = std::max(1, atoi(g));
   memset(&e->stats, 0, sizeof e->stats);
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess) {
@@ -331,6 +370,9 @@ void dis_destroy(dis_engine* e) {
   e->stage.release();
   e->out.release(); e->counters.release();
   for (cudaEvent_t ev : e->search_ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : e->gdone) cudaEventDestroy(ev);
+  for (cudaStream_t st : e->gstream) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+  if (e->fork_ev) cudaEventDestroy(e->fork_ev);
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -412,7 +454,12 @@ int dis_last_search_level_ms(dis_engine* e, int level, float* ms) {
   if (level < 0 || level >= nl || e->search_launches != nl) return fail(DIS_ERR_PARAM, "level out of range");
   CU(cudaStreamSynchronize(e->stream));
   const int i = nl - 1 - level;   // launches go coarsest -> finest
-  CU(cudaEventElapsedTime(ms, e->search_ev[2 * i], e->search_ev[2 * i + 1]));
+  *ms = 0.f;
+  for (int g = 0; g < e->n_groups; ++g) {   // groups run concurrently: this is the sum of their device times
+    float t = 0.f;
+    CU(cudaEventElapsedTime(&t, e->search_ev[2 * (g * nl + i)], e->search_ev[2 * (g * nl + i) + 1]));
+    *ms += t;
+  }
   return DIS_OK;
 }
 
@@ -421,13 +468,13 @@ int dis_last_search_ms(dis_engine* e, float* ms, int* launches) {
   if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
   CU(cudaStreamSynchronize(e->stream));
   float total = 0.f;
-  for (int i = 0; i < e->search_launches; ++i) {
+  for (int i = 0; i < e->search_launches * e->n_groups; ++i) {
     float t = 0.f;
     CU(cudaEventElapsedTime(&t, e->search_ev[2 * i], e->search_ev[2 * i + 1]));
     total += t;
   }
   *ms = total;
-  if (launches) *launches = e->search_launches;
+  if (launches) *launches = e->search_launches * e->n_groups;
   return DIS_OK;
 }
 

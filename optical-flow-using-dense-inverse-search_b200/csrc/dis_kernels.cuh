@@ -42,6 +42,7 @@ struct SearchArgs {
   int width, height, pad, tmp_w;
   int npw, nph, offw, offh, steps, np;
   int warps_per_pair;
+  int share;                // this launch may use 1/share of the GPU's resident block slots (concurrent groups)
   int iterations, patnorm;
   float lb, ub_w, ub_h;
   float out2max;            // largest fp32 s with sqrtf(s) <= outlierthresh: |start-pos| > thr <=> s > out2max

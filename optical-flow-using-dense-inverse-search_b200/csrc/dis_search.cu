@@ -568,7 +568,8 @@ int launch_ps(const SearchArgs& a, cudaStream_t s) {
   // persistent warps: lanes fetch patches from a global counter until the level is done
   const long long total = (long long)a.n_pairs * a.np;
   const long long want = (total + kWarps * 32 - 1) / (kWarps * 32);
-  const unsigned blocks = (unsigned)(want < 148 * kBlocksPerSM ? want : 148 * kBlocksPerSM);
+  const long long slots = (148 * kBlocksPerSM + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
+  const unsigned blocks = (unsigned)(want < slots ? want : slots);
   int n = 1;
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) cudaMemsetAsync(a.straggler_count, 0, sizeof(int), s);
