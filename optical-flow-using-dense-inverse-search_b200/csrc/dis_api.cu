@@ -79,7 +79,8 @@ struct dis_engine {
   bool keep_iters = true;
   int max_groups = 1;                   // DIS_GROUPS overrides; measured: no gain on B200 (levels are work-bound, not tail-bound)
 
-  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers, stage;
+  DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers, stage, walk;
+  size_t walk_patches = 0;              // capacity of `walk` in patches (largest level x pairs)
   int straggler_cap = 0;
   dis::LevelPlanes planes[16];          // by absolute scale
   size_t plane_elems[16];
@@ -179,6 +180,9 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
     e->straggler_cap = (int)std::min<size_t>(maxp / 8 + 4096, (size_t)1 << 28);
     e->straggler_stride = (64 + (size_t)e->straggler_cap * 20 + 255) & ~(size_t)255;
     if (e->stragglers.ensure(kMaxGroups * e->straggler_stride)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stragglers) failed");
+    // hand-off between the two phases of a level: 32-byte records first, then the seed entries
+    e->walk_patches = (maxp + 7) & ~(size_t)7;
+    if (e->walk.ensure(e->walk_patches * dis::kWalkBytesPerPatch)) return fail(DIS_ERR_ALLOC, "cudaMalloc(walk hand-off) failed");
   }
   return DIS_OK;
 }
@@ -210,6 +214,8 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
     a.work_counter = reinterpret_cast<int*>(sbase) + 8;
     a.stragglers = sbase + 64;
     a.straggler_cap = e->straggler_cap;
+    a.walk_state = e->walk.as<char>() + 32 * (size_t)I.num_patches * p0;
+    a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * I.num_patches * p0;
     a.n_pairs = p1 - p0;
     a.share = e->n_groups;
     a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
@@ -273,10 +279,10 @@ int fetch_counters(dis_engine* e) {
   CU(cudaMemcpyAsync(c, e->counters.p, sizeof c, cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
 #ifdef DIS_DEBUG_STATS
-  fprintf(stderr, "[dis debug] walker warps %llu: chunks/warp %.1f, cycles/warp %.0f | requests/lane %.1f, rtt cycles %.0f | "
-                  "sampler warps %llu: batches/warp %.1f, fill %.2f, busy cycles/batch %.0f, busy share %.3f | running lanes/chunk %.1f\n",
-          c[12], (double)c[4] / c[12], (double)c[5] / c[12], (double)c[11] / (32.0 * c[12]), (double)c[10] / (c[11] ? c[11] : 1),
-          c[13], (double)c[6] / c[13], (double)c[7] / (c[6] ? c[6] : 1), (double)c[8] / (c[6] ? c[6] : 1), (double)c[8] / (c[9] ? c[9] : 1), (double)c[14] / (c[4] ? c[4] : 1));
+  fprintf(stderr, "[dis debug] walk: warp-iterations %llu | running lanes/iter %.2f free lanes/iter %.2f | passes advanced per running lane-chunk %.2f | "
+                  "service: rounds/iter %.3f, patches/round %.2f, waiting at decision/iter %.2f | slow-path hits %llu | binds %llu in %llu events (%.1f lanes/event)\n",
+          c[4], (double)c[5] / c[4], (double)c[13] / c[4], (double)c[6] / (c[5] ? c[5] : 1), (double)c[7] / c[4], (double)c[8] / (c[7] ? c[7] : 1),
+          (double)c[12] / c[4], c[9], c[10], c[11], (double)c[10] / (c[11] ? c[11] : 1));
 #endif
   e->stats.patch_iterations = c[0]; e->stats.sampled_iterations = c[1];
   e->stats.resets = c[2]; e->stats.start_oob = c[3];
@@ -366,7 +372,7 @@ void dis_destroy(dis_engine* e) {
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (Level& L : e->levels) { L.flow.release(); L.u.release(); L.iters.release(); }
-  e->frames_u8.release(); e->frames_f32.release(); e->pairs.release(); e->planes_all.release(); e->stragglers.release();
+  e->frames_u8.release(); e->frames_f32.release(); e->pairs.release(); e->planes_all.release(); e->stragglers.release(); e->walk.release();
   e->stage.release();
   e->out.release(); e->counters.release();
   for (cudaEvent_t ev : e->search_ev) cudaEventDestroy(ev);
@@ -731,7 +737,7 @@ struct dis_grid {
   int pad;
   float lb, ub_w, ub_h;
   size_t plane_elems;
-  DevBuf planes, flow_prev, init, u, dense, pair, stage;
+  DevBuf planes, flow_prev, init, u, dense, pair, stage, walk;
   std::vector<float> init_host;
   bool have_first = false, have_second = false, use_prev = false, use_override = false, searched = false;
   std::vector<float> u_host;
@@ -764,6 +770,7 @@ int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_g
       g->u.ensure(sizeof(float) * 2 * I.num_patches) ||
       g->dense.ensure(sizeof(float) * 2 * (size_t)width * height) || g->pair.ensure(64) ||
       g->init.ensure(sizeof(float) * 2 * I.num_patches) ||
+      g->walk.ensure(dis::kWalkBytesPerPatch * (size_t)I.num_patches) ||
       g->flow_prev.ensure(sizeof(float) * 2 * (size_t)(width / 2 + 1) * (height / 2 + 1))) {
     dis_grid_destroy(g);
     return fail(DIS_ERR_ALLOC, "cudaMalloc(grid) failed");
@@ -779,7 +786,7 @@ void dis_grid_destroy(dis_grid* g) {
   cudaSetDevice(g->e->device);
   cudaStreamSynchronize(g->e->stream);
   g->planes.release(); g->flow_prev.release(); g->init.release(); g->u.release(); g->dense.release(); g->pair.release();
-  g->stage.release();
+  g->stage.release(); g->walk.release();
   delete g;
 }
 
@@ -846,6 +853,8 @@ int dis_grid_inverse_search(dis_grid* g) {
   a.flow_prev = g->use_prev ? g->flow_prev.as<float>() : nullptr;
   a.init_override = g->use_override ? g->init.as<float>() : nullptr;
   a.u_out = g->u.as<float>();
+  a.walk_state = g->walk.p;
+  a.walk_seeds = g->walk.as<char>() + 32 * (size_t)I.num_patches;
   a.n_pairs = 1;
   a.width = I.width; a.height = I.height; a.pad = g->pad; a.tmp_w = I.tmp_w;
   a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;

@@ -37,6 +37,8 @@ struct SearchArgs {
   void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
   int* straggler_count;     // number of entries (device)
   int* work_counter;        // next patch index of the launch (device; zeroed by the launcher)
+  void* walk_state;         // [n_pairs*np] 32-byte hand-off records of the convergence phase
+  void* walk_seeds;         // [n_pairs*np][kWalkSeeds] uint4 {pos bits x, y, delta_u x, y}
   int straggler_cap;
   int n_pairs;
   int width, height, pad, tmp_w;
@@ -55,6 +57,9 @@ struct DensifyArgs {
   size_t dense_stride;      // floats per pair
   int n_pairs, width, height, npw, nph, offw, offh, steps, np, ps;
 };
+
+constexpr int kWalkSeeds = 16;
+constexpr size_t kWalkBytesPerPatch = 32 + 16 * kWalkSeeds;   // walk_state + walk_seeds
 
 // host-callable launchers (each returns the number of kernels launched)
 int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s);

@@ -7,36 +7,33 @@
 //   Patch::inverse_search(_start) src/patch.cpp:119-203      the iteration loop
 //   Patch::get_patch_second_image src/patch.cpp:207-267      4-tap resample + mean normalisation
 //
-// Design (B200-first, not a translation):
-//  * PERSISTENT warps, one LANE per patch ("walker").  A lane carries the scalar state of its patch
-//    (u, pos, LU factors); when the patch finishes the lane is re-bound to the next patch index of a
-//    global counter, so a warp never idles behind its slowest patch and the patches of a warp are
-//    at mixed phases (which keeps the service rounds below full).
-//  * The expensive part of a pass (ps^2 4-tap samples + three tree reductions) is done by a
-//    sub-group of SG lanes per patch (SG = 4 for ps <= 8, else 8), 32/SG patches per warp round.
-//    Lane j of a sub-group owns the elements e with e mod 8 in {j, j+4} (SG 4) or {j} (SG 8), which
-//    makes Eigen's SSE reduction tree (App. A.3) exactly "serial over the lane's elements, then
-//    [in-lane add | xor-shuffle 4], xor-shuffle 2, 1".
-//  * EXACT memoisation: within a patch, delta_u is a pure function of the bit pattern of the
-//    sampling position (H, the template and the image are constant), and so is the outcome of the
-//    reset test.  Each patch keeps a 16-entry cache {pos bits -> delta_u} in shared memory, 4 sets
-//    (low bit of x, low bit of y) x 4 ways, one uint4 {bx, by, dx, dy} per entry.  A pass whose
-//    position is cached costs ~15 scalar instructions instead of ~1000.  The fp32 orbit of a patch
-//    revisits a few positions (it jitters at the ulp of the coordinate), so ~98 % of the
-//    reference's 1001 passes per patch hit.  Results are bit-identical to running every pass:
-//    nothing is approximated, only recomputation is skipped.
-//  * Way prediction: an entry is inserted at the way named by bit 1 of x and y, so the hot loop
-//    probes ONE slot (a single LDS.128); the other three ways of the set are probed once per chunk
-//    of kChunk passes, for the lanes that fell out of the fast loop.
-//  * Lanes that miss (and freshly bound lanes, which need their template's Hessian) wait; at the end
-//    of each chunk the warp serves them in rounds (one patch per sub-group).  Sub-groups leave their
-//    sums in shared memory; the owners then run the reset test / LU solve / cache insert once, in
-//    parallel.
-//  * Patches whose orbit never settles (~0.6 %) sample on every pass; after kStreakLimit such passes
-//    they are handed to k_stragglers, which packs 32/SG of them per warp with the template in
-//    registers.
-//  (tools/micro/ keeps the measured alternatives: tile-bound warps, and warp-specialised
-//  walker/sampler blocks with a shared-memory request queue; DESIGN.md has the numbers.)
+// Design (B200-first, not a translation).  A level runs as three kernels on one stream:
+//  1. k_converge — the first kN1 passes of every patch visit almost only NEW positions, so they are
+//     computed without memoisation by a sub-group of SG lanes per patch (SG = 4 for ps <= 8, else 8),
+//     32/SG patches per warp in lock step.  Lane j of a sub-group owns the elements e with e mod 8 in
+//     {j, j+4} (SG 4) or {j} (SG 8), which makes Eigen's SSE reduction tree (App. A.3) exactly "serial
+//     over the lane's elements, then [in-lane add | xor-shuffle 4], xor-shuffle 2, 1".  Template
+//     gradients, LU factors and (ps 8) the 9x9 tap window live in registers — a patch keeps the same
+//     integer tap base for nearly all its passes — so a pass is pure fp32 arithmetic.  The kernel leaves
+//     {u, k, LU} and a ready-made 16-entry cache image per patch in HBM (288 B per patch).
+//  2. k_inverse_search (the walk) — EXACT memoisation: within a patch, delta_u is a pure function of
+//     the bit pattern of the sampling position (H, the template and the image are constant), and so
+//     is the outcome of the reset test.  After convergence the fp32 orbit of a patch jitters among a
+//     few positions, so ~99 % of the remaining ~980 passes are cache hits.  PERSISTENT warps, one LANE
+//     per patch: a lane carries the scalar state of its patch and a 16-entry cache {pos bits ->
+//     delta_u} in shared memory (4 sets x 4 ways, one uint4 per entry); a hit costs ~14 scalar
+//     instructions instead of ~1000.  Way prediction: an entry is inserted at the way named by bit 1 of
+//     x and y, so the hot loop probes ONE slot (a single LDS.128); the other three ways are probed once
+//     per chunk of kChunk passes, for the lanes that fell out of the fast loop.  Lanes that miss wait;
+//     the warp serves them in rounds (one patch per sub-group; ps 8 uses 8-lane sub-groups here, which
+//     fit 80 registers and so 24 warps per SM).  A finished lane is re-bound to the next patch index of
+//     a global counter, so a warp never idles behind its slowest patch.  Results are bit-identical to
+//     running every pass: nothing is approximated, only recomputation is skipped.
+//  3. k_stragglers — patches whose orbit never settles (~0.6 %) sample on every pass; after
+//     kStreakLimit such passes the walk hands them over, and they finish here with template and tap
+//     window in registers, 32/SG per warp.
+//  (tools/micro/ keeps the measured alternatives: single-kernel designs with tile-bound warps, and
+//  warp-specialised walker/sampler blocks with a shared-memory request queue; DESIGN.md has the numbers.)
 #include <stdlib.h>
 
 #include "dis_kernels.cuh"
@@ -45,7 +42,19 @@ namespace dis {
 namespace {
 
 constexpr int kSlots = 16;            // cache entries per patch
-constexpr int kChunk = 8;             // fast-probe passes between two warp-level decisions
+#ifndef DIS_CHUNK
+#define DIS_CHUNK 8
+#endif
+#ifndef DIS_AGE
+#define DIS_AGE 4
+#endif
+#ifndef DIS_N1
+#define DIS_N1 24
+#endif
+#ifndef DIS_REBIND_MIN
+#define DIS_REBIND_MIN 4
+#endif
+constexpr int kChunk = DIS_CHUNK;           // fast-probe passes between two warp-level decisions
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kHandoffMinIter = 48;   // never hand off a patch that is still in its convergence phase
 
@@ -92,6 +101,13 @@ __device__ __forceinline__ float tree_sum(const float (&v)[Geom<PS, SG>::NPL]) {
 }
 
 struct Straggler { int pair, pid, k; float ux, uy; };
+
+// Hand-off record between the two phases of a level (k_converge -> k_inverse_search), 32 bytes.
+// k < 0: the patch finished in the first phase (its u is already in u_out).
+struct WalkState { float ux, uy; int k, swap; float p, q, l, u11; };
+constexpr int kN1 = DIS_N1;              // passes of the convergence phase (every one samples)
+static_assert(kSlots == kWalkSeeds, "hand-off layout");
+constexpr int kSeed = 16;             // the last kSeed passes of the convergence phase seed the walk phase's cache
 
 // 2x2 partial-pivot LU of the constant Hessian (src/patch.cpp:176; App. A.3)
 struct LU2 {
@@ -162,6 +178,35 @@ __device__ __forceinline__ float3 hessian_sums(const float2 (&T)[Geom<PS, SG>::N
   return make_float3(tree_sum<PS, SG>(a), tree_sum<PS, SG>(b), tree_sum<PS, SG>(c));
 }
 
+// Tap base of Patch::get_patch_second_image (src/patch.cpp:222-234), clamped into the padded plane so
+// that a position the reset test is about to reject cannot address outside it.
+template <int PS>
+__device__ __forceinline__ int2 tap_base(float opx, float opy, int pad, int wmax, int hmax) {
+  int bxi = (int)ceilf(opx + .00001f) + pad;
+  int byi = (int)ceilf(opy + .00001f) + pad;
+  bxi = min(max(bxi, PS / 2 + 1), wmax);
+  byi = min(max(byi, PS / 2 + 1), hmax);
+  return make_int2(bxi, byi);
+}
+
+// Mean normalisation (src/patch.cpp:264-266) of the lane's samples v, then the two
+// products-and-sums of src/patch.cpp:171-172 with the template gradients T.
+template <int PS, int SG>
+__device__ __forceinline__ float2 normalise_and_project(float (&v)[Geom<PS, SG>::NPL], int patnorm,
+                                                        const float2 (&T)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
+  if (patnorm) {   // x / 2^n == x * 2^-n bit for bit
+    const float sum = tree_sum<PS, SG>(v);
+    const float mean = G::POW2 ? sum * (1.0f / (float)G::NE) : sum / (float)G::NE;
+#pragma unroll
+    for (int i = 0; i < G::NPL; ++i) v[i] -= mean;
+  }
+  float px[G::NPL], py[G::NPL];
+#pragma unroll
+  for (int i = 0; i < G::NPL; ++i) { px[i] = T[i].x * v[i]; py[i] = T[i].y * v[i]; }
+  return make_float2(tree_sum<PS, SG>(px), tree_sum<PS, SG>(py));
+}
+
 // Patch::get_patch_second_image (src/patch.cpp:207-267) for the lane's elements, followed by
 // the two products-and-sums of src/patch.cpp:171-172.  T: the lane's template gradients.
 // Returns (sum gx*r, sum gy*r), identical in all lanes of the sub-group.
@@ -176,11 +221,8 @@ __device__ __forceinline__ float2 sample_and_project(const float* __restrict__ i
   const float w0 = (1 - a) * (1 - b), w1 = a * (1 - b), w2 = b * (1 - a), w3 = a * b;
   // tap base; clamped so that a position about to be rejected by the reset test (out of bounds,
   // NaN) cannot address outside the plane — its result is discarded by the owner
-  int bxi = (int)ceilf(opx + .00001f) + pad;
-  int byi = (int)ceilf(opy + .00001f) + pad;
-  bxi = min(max(bxi, PS / 2 + 1), wmax);
-  byi = min(max(byi, PS / 2 + 1), hmax);
-  const float* __restrict__ ib = imB + byi * tw + bxi;
+  const int2 tb = tap_base<PS>(opx, opy, pad, wmax, hmax);
+  const float* __restrict__ ib = imB + tb.y * tw + tb.x;
   float v[G::NPL];
   if (PS == 8) {
     // the lane owns whole columns: consecutive rows share taps, 9 x 2 loads per column instead of 8 x 4
@@ -200,16 +242,42 @@ __device__ __forceinline__ float2 sample_and_project(const float* __restrict__ i
       v[i] = ((w3 * __ldg(t) + w2 * __ldg(t - 1)) + w1 * __ldg(t - tw)) + w0 * __ldg(t - tw - 1);
     }
   }
-  if (patnorm) {   // src/patch.cpp:264-266; x / 2^n == x * 2^-n bit for bit
-    const float sum = tree_sum<PS, SG>(v);
-    const float mean = G::POW2 ? sum * (1.0f / (float)G::NE) : sum / (float)G::NE;
+  return normalise_and_project<PS, SG>(v, patnorm, T);
+}
+
+// ps == 8 with the tap window of the patch held in REGISTERS (k_converge): a patch keeps the same
+// integer tap base for almost all of its passes (1.3 distinct bases per patch on the Sintel-shape
+// workload), so the 9 x 2 x H taps of the lane's columns are loaded once and only the weights change.
+template <int SG>
+struct Window8 {
+  static constexpr int H = 8 / SG;
+  float t0[H][9], t1[H][9];
+  int bx, by;                                  // the (clamped) tap base the registers hold; -1: nothing loaded
+  __device__ __forceinline__ void load(const float* __restrict__ imB, int tw, int sl, int bxi, int byi) {
+    bx = bxi; by = byi;
 #pragma unroll
-    for (int i = 0; i < G::NPL; ++i) v[i] -= mean;
+    for (int h = 0; h < H; ++h) {
+      const float* col = imB + byi * tw + bxi + (sl + 4 * h - 4) - 5 * tw;
+#pragma unroll
+      for (int r = 0; r < 9; ++r) { t0[h][r] = __ldg(col + r * tw - 1); t1[h][r] = __ldg(col + r * tw); }
+    }
   }
-  float px[G::NPL], py[G::NPL];
+};
+
+template <int SG>
+__device__ __forceinline__ float2 sample_window8(const Window8<SG>& Wn, float opx, float opy, int patnorm,
+                                                 const float2 (&T)[Geom<8, SG>::NPL]) {
+  using G = Geom<8, SG>;
+  const float fl = floorf(opx), fk = floorf(opy);
+  const float a = opx - fl, b = opy - fk;
+  const float w0 = (1 - a) * (1 - b), w1 = a * (1 - b), w2 = b * (1 - a), w3 = a * b;
+  float v[G::NPL];
 #pragma unroll
-  for (int i = 0; i < G::NPL; ++i) { px[i] = T[i].x * v[i]; py[i] = T[i].y * v[i]; }
-  return make_float2(tree_sum<PS, SG>(px), tree_sum<PS, SG>(py));
+  for (int h = 0; h < G::H; ++h)
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+      v[8 * h + r] = ((w3 * Wn.t1[h][r + 1] + w2 * Wn.t0[h][r + 1]) + w1 * Wn.t1[h][r]) + w0 * Wn.t0[h][r];
+  return normalise_and_project<8, SG>(v, patnorm, T);
 }
 
 // The reset test of src/patch.cpp:185-194 (plus NaN => reset).
@@ -221,12 +289,40 @@ __device__ __forceinline__ bool must_reset(float px, float py, float stx, float 
   return !(s <= A.out2max) || px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py;
 }
 
-enum : int { ST_RUN = 0, ST_WAIT = 1, ST_HESS = 2, ST_FREE = 3 };
+// Insert {position bits -> delta_u} into a patch's 16-slot cache image (slot s at cache[s * STRIDE]).
+// The entry goes to the way predicted by bit 1 of x and y; an entry already there moves to the set's
+// FIFO victim way.  DEDUP: skip the insertion when the position is already present in its set.
+template <int STRIDE, bool DEDUP>
+__device__ __forceinline__ void cache_insert(uint4* cache, unsigned& fifo, const uint4 e) {
+  const int p = ((e.x & 3) << 2) | (e.y & 3);
+  const uint4 old = cache[p * STRIDE];
+  if (DEDUP) {
+    if (old.x == e.x && old.y == e.y) return;
+    const uint4 e1 = cache[(p ^ 8) * STRIDE], e2 = cache[(p ^ 2) * STRIDE], e3 = cache[(p ^ 10) * STRIDE];
+    if ((e1.x == e.x && e1.y == e.y) || (e2.x == e.x && e2.y == e.y) || (e3.x == e.x && e3.y == e.y)) return;
+  }
+  if (old.x != 0xffffffffu) {
+    const int set = ((p >> 1) & 2) | (p & 1);
+    const int way = (fifo >> (2 * set)) & 3;
+    fifo = (fifo & ~(3u << (2 * set))) | (((way + 1) & 3) << (2 * set));
+    const int q = (p & 5) | ((way & 2) << 2) | ((way & 1) << 1);
+    if (q != p) cache[q * STRIDE] = old;                      // the displaced entry moves there
+  }
+  cache[p * STRIDE] = e;
+}
+
+enum : int { ST_RUN = 0, ST_WAIT = 1, ST_FREE = 3 };
 
 constexpr int kWarps = 8;            // warps per block (independent of one another)
-constexpr int kBlocksPerSM = 2;      // 16 warps per SM at <= 128 registers: a third block would spill into the hot loops
+#ifndef DIS_WALK_SG8
+#define DIS_WALK_SG8 1
+#endif
+// Resident blocks per SM of the walk kernel.  ps 8 serves its (rare) misses with 8-lane sub-groups: 8 elements
+// per lane fit 85 registers, so three blocks (24 warps) hide the LDS -> compare -> add chain of the fast loop;
+// the other patch sizes need 128 registers for their service rounds.
+constexpr int walk_blocks(int ps, int sg) { return (ps == 8 && sg == 8) ? 3 : 2; }
 constexpr int kStreakLimit = 64;     // consecutive first-seen positions before a patch is handed off
-constexpr int kRebindMin = 4;        // free lanes a warp gathers before it fetches new patches
+constexpr int kRebindMin = DIS_REBIND_MIN;       // free lanes a warp gathers before it fetches new patches
 
 // per-warp shared memory
 struct WarpSmem {
@@ -247,8 +343,145 @@ __device__ __forceinline__ PatchGeom patch_geom(const SearchArgs& A, int idx) {
   return g;
 }
 
+// Initial displacement of a patch (PatchGrid::patch_init_from_prev_flow, src/patch_grid.cpp:108-119;
+// or the explicit per-patch init of the PatchGrid-level API).
+__device__ __forceinline__ float2 patch_init(const SearchArgs& A, int idx, int pair, float refx, float refy) {
+  if (A.init_override) return reinterpret_cast<const float2*>(A.init_override)[idx];
+  if (A.flow_prev) {
+    const int fx = (int)floorf(refx / 2), fy = (int)floorf(refy / 2);
+    const float2 v = reinterpret_cast<const float2*>(A.flow_prev + (size_t)pair * A.flow_prev_stride)[fy * (A.width / 2) + fx];
+    return make_float2(v.x * 2, v.y * 2);
+  }
+  return make_float2(0.f, 0.f);
+}
+
+// ---- phase 1: convergence ------------------------------------------------------------------------
+// The first kN1 passes of every patch visit (almost only) new positions, so they are run without any
+// memoisation by one sub-group of SG lanes per patch, G patches per warp, in lock step: template
+// gradients, LU factors and (ps 8) the tap window stay in registers, a pass is pure fp32 arithmetic.
+// Patches that end here (start out of bounds, reset, max_iter < kN1, conv_eps) are written out;
+// the others leave {u, k, LU} and their last kSeed {position -> delta_u} pairs for the walk phase.
+constexpr int kConvWarps = 4;
 template <int PS, int SG, bool FAST>
-__global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
+__global__ void __launch_bounds__(kConvWarps * 32) k_converge(const SearchArgs A) {
+  using G = Geom<PS, SG>;
+  const int lane = threadIdx.x & 31, sub = lane / SG, sl = lane % SG;
+  const int gwarp = blockIdx.x * kConvWarps + (threadIdx.x >> 5);
+  const int nwarps = gridDim.x * kConvWarps;
+  const int tw = A.tmp_w;
+  const int total = A.n_pairs * A.np;
+  const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
+  const int iters = A.iterations;
+  int eoff[G::NPL];
+  element_offsets<PS, SG>(sl, tw, eoff);
+  WalkState* __restrict__ states = reinterpret_cast<WalkState*>(A.walk_state);
+  uint4* __restrict__ seeds = reinterpret_cast<uint4*>(A.walk_seeds);
+  __shared__ uint4 images[kConvWarps][G::G * kSlots];         // the walk phase's cache image of each patch
+  uint4* img_warp = images[threadIdx.x >> 5];
+  uint4* img = img_warp + sub * kSlots;
+  unsigned long long c_iters = 0;
+  unsigned c_sampled = 0, c_resets = 0, c_oob = 0;
+#pragma unroll 1
+  for (int base = gwarp * G::G; base < total; base += nwarps * G::G) {
+    const bool have = base + sub < total;
+    const int idx = have ? base + sub : total - 1;
+    const PatchGeom g = patch_geom(A, idx);
+    const float refx = (float)g.rx, refy = (float)g.ry;
+    const float2 in = patch_init(A, idx, g.pair, refx, refy);
+    float ux = in.x, uy = in.y;                               // Patch::inverse_search_start, src/patch.cpp:119-154
+    float px = refx + ux, py = refy + uy;
+    const float stx = px, sty = py;
+    const bool oob = px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py;
+    bool active = have && !oob;
+    bool was_reset = false;
+    const int2 fr = A.pairs[g.pair];
+    const float2* __restrict__ gxyA =
+        reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
+    const float* __restrict__ imB = A.planes.base + (size_t)fr.y * A.planes.frame_stride;
+    float2 T[G::NPL];
+    load_template<PS, SG>(gxyA, (g.ry + A.pad) * tw + (g.rx + A.pad), tw, sl, eoff, T);
+    LU2 lu;
+    {
+      const float3 h = hessian_sums<PS, SG>(T);               // compute_hessian_matrix, src/patch.cpp:75-91
+      float h00 = h.x, h11 = h.z;
+      fix_singular(h00, h.y, h11);
+      lu.factor(h00, h.y, h11);
+    }
+    Window8<SG> Wn;
+    Wn.bx = -1; Wn.by = -1;
+    int k = 0;
+    unsigned ns = 0, fifo = 0;
+    __syncwarp();
+#pragma unroll
+    for (int i = lane; i < G::G * kSlots; i += 32) img_warp[i] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
+    __syncwarp();
+#pragma unroll 1
+    for (int pass = 0;; ++pass) {
+      if (active) {
+        if (must_reset(px, py, stx, sty, A)) { ux = in.x; uy = in.y; was_reset = true; active = false; }   // src/patch.cpp:185-194
+        else if (k > iters) active = false;                                                              // src/patch.cpp:199-201
+      }
+      if (pass == kN1 || !__any_sync(kFull, active)) break;
+      float2 sg;
+      if constexpr (PS == 8) {
+        const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
+        if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) Wn.load(imB, tw, sl, tb.x, tb.y);
+        sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
+      } else {
+        sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
+      }
+      if (active) {
+        const float2 d = lu.solve(sg.x, sg.y);                // src/patch.cpp:176
+        if (sl == 0 && pass >= kN1 - kSeed)
+          cache_insert<1, true>(img, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y)));
+        ++k; ++ns;
+        ux = ux - d.x; uy = uy - d.y;                         // src/patch.cpp:179
+        px = refx + ux; py = refy + uy;                       // src/patch.cpp:182
+        if (FAST) { if (d.x * d.x + d.y * d.y < A.conv_eps2) active = false; }
+      }
+    }
+    __syncwarp();
+    if (__any_sync(kFull, active)) {                          // cache images of the batch's patches, coalesced
+#pragma unroll
+      for (int i = lane; i < G::G * kSlots; i += 32)
+        if (base + i / kSlots < total) seeds[(size_t)base * kSlots + i] = img_warp[i];
+    }
+    if (have && sl == 0) {
+      WalkState ws;
+      ws.ux = ux; ws.uy = uy; ws.k = active ? k : -1; ws.swap = (lu.swap ? 1 : 0) | (int)(fifo << 8);
+      ws.p = lu.p; ws.q = lu.q; ws.l = lu.l; ws.u11 = lu.u11;
+      reinterpret_cast<float4*>(states)[2 * (size_t)idx] = make_float4(ws.ux, ws.uy, __int_as_float(ws.k), __int_as_float(ws.swap));
+      reinterpret_cast<float4*>(states)[2 * (size_t)idx + 1] = make_float4(ws.p, ws.q, ws.l, ws.u11);
+      c_sampled += ns;
+      if (!active) {                                          // finished here: Patch::get_u_vector
+        reinterpret_cast<float2*>(A.u_out)[idx] = make_float2(ux, uy);
+        if (A.iters_out) A.iters_out[idx] = k;
+        c_iters += (unsigned long long)k;
+        c_resets += was_reset ? 1u : 0u;
+        c_oob += oob ? 1u : 0u;
+      }
+    }
+  }
+  if (A.counters) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      c_iters += __shfl_xor_sync(kFull, c_iters, o);
+      c_sampled += __shfl_xor_sync(kFull, c_sampled, o);
+      c_resets += __shfl_xor_sync(kFull, c_resets, o);
+      c_oob += __shfl_xor_sync(kFull, c_oob, o);
+    }
+    if (lane == 0 && (c_iters | c_sampled | c_resets | c_oob)) {
+      atomicAdd(&A.counters[0], c_iters);
+      atomicAdd(&A.counters[1], (unsigned long long)c_sampled);
+      atomicAdd(&A.counters[2], (unsigned long long)c_resets);
+      atomicAdd(&A.counters[3], (unsigned long long)c_oob);
+    }
+  }
+}
+
+// ---- phase 2: the walk ---------------------------------------------------------------------------
+template <int PS, int SG, bool FAST>
+__global__ void __launch_bounds__(kWarps * 32, walk_blocks(PS, SG))
 k_inverse_search(const SearchArgs A) {
   using G = Geom<PS, SG>;
   extern __shared__ uint4 smem_raw[];
@@ -287,33 +520,34 @@ k_inverse_search(const SearchArgs A) {
       if (lane == leader) base = atomicAdd(A.work_counter, __popc(free_m));
       base = __shfl_sync(kFull, base, leader);
       if (base + __popc(free_m) >= total) exhausted = true;
+#ifdef DIS_DEBUG_STATS
+      if (lane == leader) { atomicAdd(&A.counters[10], (unsigned long long)__popc(free_m)); atomicAdd(&A.counters[11], 1ull); }
+#endif
       if (state == ST_FREE) {
         idx = base + __popc(free_m & ((1u << lane) - 1u));
         if (idx < total) {
-          const PatchGeom g = patch_geom(A, idx);
-          pair = g.pair;
-          coff = (g.ry + A.pad) * tw + (g.rx + A.pad);
-          refx = (float)g.rx; refy = (float)g.ry;
-          inx = 0.f; iny = 0.f;                              // src/patch_grid.cpp:108-119
-          if (A.init_override) {
-            const float2 v = reinterpret_cast<const float2*>(A.init_override)[idx];
-            inx = v.x; iny = v.y;
-          } else if (A.flow_prev) {
-            const int fx = (int)floorf(refx / 2), fy = (int)floorf(refy / 2);
-            const float2 v = reinterpret_cast<const float2*>(A.flow_prev + (size_t)g.pair * A.flow_prev_stride)[fy * (A.width / 2) + fx];
-            inx = v.x * 2; iny = v.y * 2;
-          }
-          ux = inx; uy = iny;                                // Patch::inverse_search_start, src/patch.cpp:119-154
-          px = refx + ux; py = refy + uy;
-          stx = px; sty = py;
-          k = 0; fifo = 0; streak = 0; k_posted = -2; was_reset = false; waited = 0;
+          const float4 w0 = reinterpret_cast<const float4*>(A.walk_state)[2 * (size_t)idx];
+          k = __float_as_int(w0.z);
+          if (k >= 0) {                                        // else: finished in k_converge
+            const float4 w1 = reinterpret_cast<const float4*>(A.walk_state)[2 * (size_t)idx + 1];
+            const PatchGeom g = patch_geom(A, idx);
+            pair = g.pair;
+            coff = (g.ry + A.pad) * tw + (g.rx + A.pad);
+            refx = (float)g.rx; refy = (float)g.ry;
+            const float2 in = patch_init(A, idx, g.pair, refx, refy);
+            inx = in.x; iny = in.y;
+            stx = refx + inx; sty = refy + iny;                // Patch::inverse_search_start, src/patch.cpp:119-154
+            ux = w0.x; uy = w0.y;
+            px = refx + ux; py = refy + uy;
+            lu.p = w1.x; lu.q = w1.y; lu.l = w1.z; lu.u11 = w1.w;
+            lu.swap = (__float_as_int(w0.w) & 1) != 0;
+            fifo = (unsigned)__float_as_int(w0.w) >> 8;
+            streak = 0; k_posted = -2; was_reset = false; waited = 0;
+            const uint4* __restrict__ seed = reinterpret_cast<const uint4*>(A.walk_seeds) + (size_t)idx * kSlots;
 #pragma unroll
-          for (int s = 0; s < kSlots; ++s) cache[s * 32] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
-          if (px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py) {
-            ++c_oob;                                         // start out of bounds: u = init, 0 passes
-            reinterpret_cast<float2*>(A.u_out)[idx] = make_float2(ux, uy);
-            if (A.iters_out) A.iters_out[idx] = 0;
-          } else state = ST_HESS;                            // first the template's Hessian (a service round)
+            for (int s = 0; s < kSlots; ++s) cache[s * 32] = __ldg(seed + s);   // the cache image k_converge built
+            state = ST_RUN;
+          }
         }
       }
     }
@@ -322,6 +556,12 @@ k_inverse_search(const SearchArgs A) {
     //      miss (or when it is done) and idles until the chunk ends -----------------------------------
     bool run = state == ST_RUN;
     bool fin = false;                                        // the lane's patch is finished in this round
+#ifdef DIS_DEBUG_STATS
+    const int dbg_k0 = k;
+    if (lane == 0) { atomicAdd(&A.counters[4], 1ull); }
+    { const unsigned m = __ballot_sync(kFull, run), f = __ballot_sync(kFull, state == ST_FREE);
+      if (lane == 0) { atomicAdd(&A.counters[5], (unsigned long long)__popc(m)); atomicAdd(&A.counters[13], (unsigned long long)__popc(f)); } }
+#endif
 #pragma unroll
     for (int it = 0; it < kChunk; ++it) {
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
@@ -335,6 +575,11 @@ k_inverse_search(const SearchArgs A) {
         if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) { run = false; fin = true; } }
       }
     }
+#ifdef DIS_DEBUG_STATS
+    { int adv = k - dbg_k0;
+      for (int o = 16; o > 0; o >>= 1) adv += __shfl_xor_sync(kFull, adv, o);
+      if (lane == 0) atomicAdd(&A.counters[6], (unsigned long long)adv); }
+#endif
     // ---- lanes that left the fast phase: probe all four ways of the set ---------------------------
     if (state == ST_RUN && !run && !fin) {
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
@@ -343,6 +588,9 @@ k_inverse_search(const SearchArgs A) {
       const bool m0 = e0.x == bx && e0.y == by, m1 = e1.x == bx && e1.y == by;
       const bool m2 = e2.x == bx && e2.y == by, m3 = e3.x == bx && e3.y == by;
       if (m0 || m1 || m2 || m3) {
+#ifdef DIS_DEBUG_STATS
+        atomicAdd(&A.counters[9], 1ull);
+#endif
         if (k > iters) fin = true;                          // src/patch.cpp:199-201 (position already vetted)
         else {
           const uint4 e = m0 ? e0 : m1 ? e1 : m2 ? e2 : e3;
@@ -376,41 +624,36 @@ k_inverse_search(const SearchArgs A) {
     // ---- service: waiting patches (first-seen positions, new templates), one per sub-group and round.
     //      Whole rounds; an under-filled last round only if it is at least half full, nothing else can
     //      run, or one of its patches has already waited a chunk. -------------------------------------
-    const bool needs = (state == ST_WAIT || state == ST_HESS) && !fin;
+    const bool needs = state == ST_WAIT && !fin;
     const unsigned wait_mask = __ballot_sync(kFull, needs);
     bool served = false;
     if (wait_mask != 0) {
       const int nwait = __popc(wait_mask);
       const int rem = nwait % G::G;
       const bool others = __ballot_sync(kFull, state == ST_RUN && !fin) != 0;
-      const bool aged = __any_sync(kFull, needs && waited > 0);
+      const bool aged = __any_sync(kFull, needs && waited >= DIS_AGE);
       const int nserv = (!others || 2 * rem >= G::G || aged) ? nwait : nwait - rem;
       const int rank = __popc(wait_mask & ((1u << lane) - 1u));
       served = needs && rank < nserv;
       if (served) W.list[rank] = lane;
+#ifdef DIS_DEBUG_STATS
+      if (lane == 0) { atomicAdd(&A.counters[7], (unsigned long long)((nserv + G::G - 1) / G::G)); atomicAdd(&A.counters[8], (unsigned long long)nserv);
+                       atomicAdd(&A.counters[12], (unsigned long long)nwait); }
+#endif
       __syncwarp();
 #pragma unroll 1
       for (int base = 0; base < nserv; base += G::G) {
         const int src = W.list[min(base + sub, nserv - 1)];
         const float opx = __shfl_sync(kFull, px, src), opy = __shfl_sync(kFull, py, src);
         const int oc = __shfl_sync(kFull, coff, src), opair = __shfl_sync(kFull, pair, src);
-        const int kind = __shfl_sync(kFull, state, src) == ST_HESS;
         const int2 fr = A.pairs[opair];
         const float2* __restrict__ gxyA =
             reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
         const float* __restrict__ imB = A.planes.base + (size_t)fr.y * A.planes.frame_stride;
         float2 T[G::NPL];
         load_template<PS, SG>(gxyA, oc, tw, sl, eoff, T);
-        float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
-        const unsigned kinds = __ballot_sync(kFull, kind != 0);
-        if (kinds != 0) {                                    // compute_hessian_matrix, src/patch.cpp:75-91
-          const float3 hs = hessian_sums<PS, SG>(T);
-          if (kind) out = make_float4(hs.x, hs.y, hs.z, 0.f);
-        }
-        if (kinds != kFull) {
-          const float2 sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, opx, opy, sl, A.patnorm, eoff, T);
-          if (!kind) out = make_float4(sg.x, sg.y, 0.f, 0.f);
-        }
+        const float2 sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, opx, opy, sl, A.patnorm, eoff, T);
+        const float4 out = make_float4(sg.x, sg.y, 0.f, 0.f);
         if (sl == 0) W.res[src] = out;
       }
       __syncwarp();
@@ -418,28 +661,13 @@ k_inverse_search(const SearchArgs A) {
     if (served) {
       const float4 g = W.res[lane];
       waited = 0;
-      if (state == ST_HESS) {
-        float h00 = g.x, h11 = g.z;
-        fix_singular(h00, g.y, h11);
-        lu.factor(h00, g.y, h11);
-        state = ST_RUN;
-      } else if (must_reset(px, py, stx, sty, A)) {          // src/patch.cpp:185-194
+      if (must_reset(px, py, stx, sty, A)) {                 // src/patch.cpp:185-194
         ux = inx; uy = iny; was_reset = true; fin = true;
       } else if (k > iters) {                                // src/patch.cpp:199-201
         fin = true;
       } else {
         const float2 d = lu.solve(g.x, g.y);                 // src/patch.cpp:176
-        const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-        const int p = ((bx & 3) << 2) | (by & 3);
-        const uint4 old = cache[p * 32];
-        if (old.x != 0xffffffffu) {                           // predicted way taken: evict the set's FIFO victim
-          const int set = ((p >> 1) & 2) | (p & 1);
-          const int way = (fifo >> (2 * set)) & 3;
-          fifo = (fifo & ~(3u << (2 * set))) | (((way + 1) & 3) << (2 * set));
-          const int q = (p & 5) | ((way & 2) << 2) | ((way & 1) << 1);
-          if (q != p) cache[q * 32] = old;                    // the displaced entry moves there
-        }
-        cache[p * 32] = make_uint4(bx, by, __float_as_uint(d.x), __float_as_uint(d.y));
+        cache_insert<32, false>(cache, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y)));
         ++c_sampled;
         ++k;
         ux = ux - d.x; uy = uy - d.y;
@@ -524,9 +752,18 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
     int k = e.k;
     bool active = have;
     unsigned was_reset = 0, ns = 0;
+    Window8<SG> Wn;
+    Wn.bx = -1; Wn.by = -1;
 #pragma unroll 1
     while (__any_sync(kFull, active)) {
-      const float2 sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
+      float2 sg;
+      if constexpr (PS == 8) {                               // tap window in registers, reloaded when the base moves
+        const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
+        if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) Wn.load(imB, tw, sl, tb.x, tb.y);
+        sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
+      } else {
+        sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
+      }
       if (active) {
         if (must_reset(px, py, stx, sty, A)) { ux = inx; uy = iny; was_reset = 1; active = false; }
         else if (k > A.iterations) active = false;
@@ -562,18 +799,24 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
 
 template <int PS, int SG, bool FAST>
 int launch_ps(const SearchArgs& a, cudaStream_t s) {
+  constexpr int WSG = (DIS_WALK_SG8 && PS == 8) ? 8 : SG;   // sub-group size of the walk phase's (rare) service rounds
   const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
-  cudaFuncSetAttribute(k_inverse_search<PS, SG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaFuncSetAttribute(k_inverse_search<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   // persistent warps: lanes fetch patches from a global counter until the level is done
   const long long total = (long long)a.n_pairs * a.np;
   const long long want = (total + kWarps * 32 - 1) / (kWarps * 32);
-  const long long slots = (148 * kBlocksPerSM + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
+  const long long slots = (148 * walk_blocks(PS, WSG) + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
   const unsigned blocks = (unsigned)(want < slots ? want : slots);
-  int n = 1;
+  int n = 2;
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) cudaMemsetAsync(a.straggler_count, 0, sizeof(int), s);
-  k_inverse_search<PS, SG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
+  {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
+    const long long cwant = (total + kConvWarps * Geom<PS, SG>::G - 1) / (kConvWarps * Geom<PS, SG>::G);
+    const long long cslots = 148LL * 12 / (a.share > 1 ? a.share : 1);
+    k_converge<PS, SG, FAST><<<(unsigned)(cwant < cslots ? cwant : cslots), kConvWarps * 32, 0, s>>>(a);
+  }
+  k_inverse_search<PS, WSG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
   if (a.stragglers) { k_stragglers<PS, SG, FAST><<<148 * 4, 128, 0, s>>>(a); ++n; }
   return n;
 }

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdis_b200.so")
+LIB_PATH = os.environ.get("DIS_B200_LIB") or os.path.join(_HERE, "libdis_b200.so")   # the override is for tuning builds (tools/variants.sh)
 
 _u8p = C.POINTER(C.c_uint8)
 _fp = C.POINTER(C.c_float)
