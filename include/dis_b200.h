@@ -50,7 +50,11 @@ typedef struct dis_params {
   /* Extension, off by default (0): stop a patch once |delta_u| < conv_eps.  The reference has no
    * convergence criterion; conv_eps > 0 is a reported deviation, never the default. */
   float conv_eps;
-  int reserved[5];
+  /* fix_parameters fields the reference derives but its inner classes take explicitly
+   * (include/optical_flow.hpp:33-35); 0 = derive them as src/optical_flow.cpp:34,38 does. */
+  int steps;             /* distance between patch centres; 0: max(1, floor(patch_size*(1-overlap))) */
+  float outlier_thresh;  /* displacement (px) beyond which a patch is reset; 0: patch_size/2 */
+  int reserved[3];
 } dis_params;
 
 typedef struct dis_engine dis_engine;   /* opaque handle */
@@ -161,6 +165,12 @@ DIS_API int dis_get_stats(dis_engine* e, dis_stats* out);
  * one to one; used by the C++ mirror classes in include/dis_b200.hpp. */
 typedef struct dis_grid dis_grid;
 DIS_API int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_grid** out);
+/* A grid of ONE patch centred at (ref_x, ref_y): the unit behind the Patch mirror class
+ * (include/patch.hpp:33-43; Patch::init_patch takes the reference point explicitly).  The
+ * reference rounds the point for the template gather (src/patch.cpp:52-53) and only ever passes
+ * integer points; non-integer points are rejected with DIS_ERR_PARAM. */
+DIS_API int dis_grid_create_single(dis_engine* e, int width, int height, int img_padding, float ref_x,
+                                   float ref_y, dis_grid** out);
 DIS_API void dis_grid_destroy(dis_grid* g);
 DIS_API int dis_grid_init(dis_grid* g, const float* img_first, const float* img_first_dx,
                           const float* img_first_dy);                     /* init_grid */
@@ -178,6 +188,13 @@ DIS_API int dis_grid_get_patch(dis_grid* g, int i, float* ref_xy, float* u_xy); 
 DIS_API int dis_write_flo(const char* path, const float* flow, int w, int h);
 DIS_API int dis_read_flo(const char* path, float* flow, int w, int h);
 DIS_API int dis_read_flo_size(const char* path, int* w, int* h);
+
+/* Middlebury colour coding, draw_optical_flow(flow, dst, maxmotion) of src/color_coding.cpp:83-117
+ * (called at src/main.cpp:200-201 with maxmotion = -1: the range is the field's own maximum).
+ * flow: h x w x 2 fp32 host; bgr_out: h x w x 3 u8 host (B,G,R as cv::Mat CV_8UC3). */
+DIS_API int dis_color_code(dis_engine* e, const float* flow, int w, int h, float maxmotion, uint8_t* bgr_out);
+/* Same for the (device-resident) cropped flow of pair `pair` of the last run. */
+DIS_API int dis_color_code_pair(dis_engine* e, int pair, float maxmotion, uint8_t* bgr_out);
 
 #ifdef __cplusplus
 }

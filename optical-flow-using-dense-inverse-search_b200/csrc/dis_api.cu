@@ -58,6 +58,7 @@ struct dis_engine {
   dis_params prm;
   int device = 0;
   int steps = 1;
+  float outlier = 4.f;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // Pairs are independent: a run is split into up to kMaxGroups groups of pairs, each with its own
@@ -98,6 +99,8 @@ int check_params(const dis_params& p) {
     return fail(DIS_ERR_PARAM, "need 0 <= finest_scale <= coarsest_scale <= 15");
   if (p.max_iter < 0) return fail(DIS_ERR_PARAM, "max_iter must be >= 0");
   if (!(p.patch_overlap >= 0.f && p.patch_overlap < 1.f)) return fail(DIS_ERR_PARAM, "patch_overlap must be in [0,1)");
+  if (p.steps < 0 || p.steps > p.patch_size) return fail(DIS_ERR_PARAM, "steps must be in [1, patch_size] (0 = derive from patch_overlap)");
+  if (!(p.outlier_thresh >= 0.f)) return fail(DIS_ERR_PARAM, "outlier_thresh must be >= 0 (0 = patch_size/2)");
   return DIS_OK;
 }
 
@@ -223,7 +226,7 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
     a.warps_per_pair = (I.num_patches + 31) / 32;
     a.iterations = p.max_iter; a.patnorm = p.patch_norm ? 1 : 0;
     a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
-    a.out2max = sq_threshold((float)p.patch_size / 2);   // outlierthresh, src/optical_flow.cpp:34
+    a.out2max = sq_threshold(e->outlier);
     a.conv_eps2 = p.conv_eps * p.conv_eps;
     cudaEvent_t* ev = &e->search_ev[2 * (g * nl + launch)];
     CU(cudaEventRecord(ev[0], st));
@@ -355,7 +358,8 @@ int dis_create(const dis_params* p, int device, dis_engine** out) {
   CU(cudaSetDevice(device));
   dis_engine* e = new dis_engine();
   e->prm = *p; e->device = device;
-  e->steps = steps_of(p->patch_size, p->patch_overlap);
+  e->steps = p->steps > 0 ? p->steps : steps_of(p->patch_size, p->patch_overlap);
+  e->outlier = p->outlier_thresh > 0.f ? p->outlier_thresh : (float)p->patch_size / 2;   // src/optical_flow.cpp:34
   if (const char* g = getenv("DIS_GROUPS")) e->max_groups = std::max(1, atoi(g));
   memset(&e->stats, 0, sizeof e->stats);
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -745,7 +749,7 @@ struct dis_grid {
 
 extern "C" {
 
-int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_grid** out) {
+static int grid_create(dis_engine* e, int width, int height, int img_padding, bool single, int ref_x, int ref_y, dis_grid** out) {
   if (!e || !out) return fail(DIS_ERR_PARAM, "null argument");
   *out = nullptr;
   if (width < 2 || height < 2) return fail(DIS_ERR_PARAM, "level too small");
@@ -762,6 +766,7 @@ int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_g
   I.nph = (int)ceilf((float)height / (float)I.steps);
   I.offw = (width - (I.npw - 1) * I.steps) / 2;
   I.offh = (height - (I.nph - 1) * I.steps) / 2;
+  if (single) { I.npw = 1; I.nph = 1; I.offw = ref_x; I.offh = ref_y; }
   I.num_patches = I.npw * I.nph;
   g->lb = -(float)ps / 2; g->ub_w = (float)(width + ps / 2 - 2); g->ub_h = (float)(height + ps / 2 - 2);
   g->plane_elems = ((size_t)I.tmp_w * I.tmp_h + 3) & ~(size_t)3;
@@ -779,6 +784,20 @@ int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_g
   g->init_host.assign(2 * (size_t)I.num_patches, 0.f);
   *out = g;
   return DIS_OK;
+}
+
+int dis_grid_create(dis_engine* e, int width, int height, int img_padding, dis_grid** out) {
+  return grid_create(e, width, height, img_padding, false, 0, 0, out);
+}
+
+int dis_grid_create_single(dis_engine* e, int width, int height, int img_padding, float ref_x, float ref_y, dis_grid** out) {
+  if (!(ref_x == floorf(ref_x) && ref_y == floorf(ref_y))) return fail(DIS_ERR_PARAM, "patch reference point must be integer valued");
+  const int half = e ? e->prm.patch_size / 2 : 0;
+  // the template gather (src/patch.cpp:47-73) must stay inside the padded plane
+  if (e && (ref_x < (float)(half - img_padding) || ref_y < (float)(half - img_padding) ||
+            ref_x > (float)(width + img_padding - half) || ref_y > (float)(height + img_padding - half)))
+    return fail(DIS_ERR_PARAM, "patch reference point outside the padded image");
+  return grid_create(e, width, height, img_padding, true, (int)ref_x, (int)ref_y, out);
 }
 
 void dis_grid_destroy(dis_grid* g) {
@@ -860,7 +879,7 @@ int dis_grid_inverse_search(dis_grid* g) {
   a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
   a.warps_per_pair = (I.num_patches + 31) / 32;
   a.iterations = e->prm.max_iter; a.patnorm = e->prm.patch_norm ? 1 : 0;
-  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.out2max = sq_threshold((float)e->prm.patch_size / 2);
+  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.out2max = sq_threshold(e->outlier);
   a.conv_eps2 = e->prm.conv_eps * e->prm.conv_eps;
   if (dis::launch_inverse_search(a, e->prm.patch_size, e->stream) < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
   CU(cudaGetLastError());
@@ -903,6 +922,39 @@ int dis_grid_get_patch(dis_grid* g, int i, float* ref_xy, float* u_xy) {
     else { u_xy[0] = 0.f; u_xy[1] = 0.f; }   // Patch::reset_patch, src/patch.cpp:102-116
   }
   return DIS_OK;
+}
+
+// ---- colour coding (src/color_coding.cpp:83-117) -------------------------------------------------
+static int color_device(dis_engine* e, const float* dflow, size_t npx, float maxmotion, uint8_t* bgr_out) {
+  const size_t off = (2 * sizeof(float) * npx + 255) & ~(size_t)255;   // stage: [flow | scratch | bgr]
+  if (e->stage.ensure(off + 256 + 3 * npx)) return fail(DIS_ERR_ALLOC, "cudaMalloc(colour stage) failed");
+  char* st = e->stage.as<char>();
+  e->launches += dis::launch_color_code(dflow, npx, maxmotion, reinterpret_cast<unsigned*>(st + off),
+                                        reinterpret_cast<uint8_t*>(st + off + 256), e->stream);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(bgr_out, st + off + 256, 3 * npx, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return DIS_OK;
+}
+
+int dis_color_code(dis_engine* e, const float* flow, int w, int h, float maxmotion, uint8_t* bgr_out) {
+  if (!e || !flow || !bgr_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (w <= 0 || h <= 0) return fail(DIS_ERR_PARAM, "empty flow field");
+  CU(cudaSetDevice(e->device));
+  const size_t npx = (size_t)w * h;
+  const size_t off = (2 * sizeof(float) * npx + 255) & ~(size_t)255;
+  if (e->stage.ensure(off + 256 + 3 * npx)) return fail(DIS_ERR_ALLOC, "cudaMalloc(colour stage) failed");
+  CU(cudaMemcpyAsync(e->stage.p, flow, 2 * sizeof(float) * npx, cudaMemcpyHostToDevice, e->stream));
+  return color_device(e, e->stage.as<float>(), npx, maxmotion, bgr_out);
+}
+
+int dis_color_code_pair(dis_engine* e, int pair, float maxmotion, uint8_t* bgr_out) {
+  if (!e || !bgr_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run || !e->out.p) return fail(DIS_ERR_STATE, "no run yet");
+  if (pair < 0 || pair >= e->n_pairs) return fail(DIS_ERR_PARAM, "pair index out of range");
+  CU(cudaSetDevice(e->device));
+  const size_t npx = (size_t)e->w0 * e->h0;
+  return color_device(e, e->out.as<float>() + 2 * npx * pair, npx, maxmotion, bgr_out);
 }
 
 // ---- Middlebury .flo (src/IO_flow.cpp:10-98) ----------------------------------------------------

@@ -87,4 +87,7 @@ int launch_crop(const float* dense, size_t dense_stride, int W, int H, int left,
 int launch_upsample_crop(const float* dense, size_t dense_stride, int Wf, int Hf, int finest, int left,
                          int top, float* out, int w, int h, int n_pairs, cudaStream_t s);
 
+// Middlebury colour coding (src/color_coding.cpp): flow [n_pixels][2] -> bgr [n_pixels][3]; scratch: one unsigned
+int launch_color_code(const float* flow, size_t n_pixels, float maxmotion, unsigned* scratch, uint8_t* bgr, cudaStream_t s);
+
 }  // namespace dis

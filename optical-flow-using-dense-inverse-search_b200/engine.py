@@ -22,7 +22,8 @@ class DisParams(C.Structure):
     """dis_params — the parameters of /root/reference/src/main.cpp:63-72."""
     _fields_ = [("max_iter", C.c_int), ("patch_size", C.c_int), ("coarsest_scale", C.c_int),
                 ("finest_scale", C.c_int), ("patch_overlap", C.c_float), ("patch_norm", C.c_int),
-                ("conv_eps", C.c_float), ("reserved", C.c_int * 5)]
+                ("conv_eps", C.c_float), ("steps", C.c_int), ("outlier_thresh", C.c_float),
+                ("reserved", C.c_int * 3)]
 
 
 class DisLevelInfo(C.Structure):
@@ -47,9 +48,10 @@ ABI_SYMBOLS = [
     "dis_run_batch_u8", "dis_run_sequence_u8", "dis_run_pyramids", "dis_construct_pyramid", "dis_upload_frames_u8",
     "dis_run_resident", "dis_download_flows", "dis_synchronize", "dis_timer_start", "dis_timer_stop_ms",
     "dis_last_search_ms", "dis_last_search_level_ms", "dis_num_levels", "dis_get_level_info", "dis_get_patches", "dis_get_level_flow",
-    "dis_get_plane", "dis_get_stats", "dis_grid_create", "dis_grid_destroy", "dis_grid_init", "dis_grid_set_target",
+    "dis_get_plane", "dis_get_stats", "dis_grid_create", "dis_grid_create_single", "dis_grid_destroy", "dis_grid_init", "dis_grid_set_target",
     "dis_grid_init_from_prev_flow", "dis_grid_set_patch_init", "dis_grid_inverse_search", "dis_grid_densify",
     "dis_grid_num_patches", "dis_grid_get_patch", "dis_write_flo", "dis_read_flo", "dis_read_flo_size",
+    "dis_color_code", "dis_color_code_pair",
 ]
 
 
@@ -118,6 +120,20 @@ class Engine:
         out = np.empty((h, w, 2), np.float32)
         _chk(self.lib.dis_run_pair_u8(self._h, a.ctypes.data_as(_u8p), b.ctypes.data_as(_u8p), w, h, w,
                                       out.ctypes.data_as(_fp)))
+        return out
+
+    def color_code(self, flow: np.ndarray, maxmotion: float = -1.0) -> np.ndarray:
+        """draw_optical_flow (/root/reference/src/color_coding.cpp:83-117): (h,w,2) fp32 -> (h,w,3) u8 B,G,R."""
+        flow = np.ascontiguousarray(flow, np.float32)
+        h, w, _ = flow.shape
+        out = np.empty((h, w, 3), np.uint8)
+        _chk(self.lib.dis_color_code(self._h, flow.ctypes.data_as(_fp), w, h, C.c_float(maxmotion), out.ctypes.data_as(_u8p)))
+        return out
+
+    def color_code_pair(self, pair: int, h: int, w: int, maxmotion: float = -1.0) -> np.ndarray:
+        """Colour coding of the device-resident flow of pair `pair` of the last run."""
+        out = np.empty((h, w, 3), np.uint8)
+        _chk(self.lib.dis_color_code_pair(self._h, pair, C.c_float(maxmotion), out.ctypes.data_as(_u8p)))
         return out
 
     def run_batch(self, a: np.ndarray, b: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:

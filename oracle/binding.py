@@ -130,6 +130,16 @@ class Oracle:
                 f(*six, pad, out.ctypes.data_as(_fp), W, H, coarsest, finest, iterations, patch_size, overlap, int(patnorm))
         return (out, d) if dump else out
 
+    def color_code(self, flow, maxmotion=-1.0):
+        """draw_optical_flow (src/color_coding.cpp:83-117) -> (h,w,3) u8 B,G,R."""
+        flow = np.ascontiguousarray(flow, np.float32)
+        h, w, _ = flow.shape
+        out = np.empty((h, w, 3), np.uint8)
+        f = self.port.oracle_color_code
+        f.argtypes = [_fp, C.c_int, C.c_int, C.c_float, C.c_void_p]
+        f(flow.ctypes.data_as(_fp), w, h, maxmotion, out.ctypes.data)
+        return out
+
     def run_pair_u8(self, a, b, iterations=1000, patch_size=8, coarsest=3, finest=0, overlap=0.7, patnorm=True,
                     dump=False):
         """Whole path of src/main.cpp:135-198 (finest == 0): pad, pyramids, engine, crop."""

@@ -437,3 +437,54 @@ ORACLE_API int oracle_run_pair_u8(const uint8_t* a, const uint8_t* b, int w, int
   free(fa); free(fb); free(full);
   return 0;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Colour coding: draw_optical_flow / compute_color / is_flow_correct,
+ * src/color_coding.cpp:8-117.  bgr is h*w*3 bytes, B,G,R per pixel (pix[2 - b], :77).
+ * ---------------------------------------------------------------------------------------- */
+static int flow_ok(float x, float y) {                       /* :8-11 */
+  return !isnan(x) && !isnan(y) && fabsf(x) < 1e9f && fabsf(y) < 1e9f;
+}
+
+ORACLE_API void oracle_color_code(const float* flow, int w, int h, float maxmotion, uint8_t* bgr) {
+  enum { RY = 15, YG = 6, GC = 4, CB = 11, BM = 13, MR = 6, NCOLS = RY + YG + GC + CB + BM + MR };
+  int wheel[NCOLS][3];
+  int k = 0;                                                 /* :30-50 */
+  for (int i = 0; i < RY; ++i, ++k) { wheel[k][0] = 255; wheel[k][1] = 255 * i / RY; wheel[k][2] = 0; }
+  for (int i = 0; i < YG; ++i, ++k) { wheel[k][0] = 255 - 255 * i / YG; wheel[k][1] = 255; wheel[k][2] = 0; }
+  for (int i = 0; i < GC; ++i, ++k) { wheel[k][0] = 0; wheel[k][1] = 255; wheel[k][2] = 255 * i / GC; }
+  for (int i = 0; i < CB; ++i, ++k) { wheel[k][0] = 0; wheel[k][1] = 255 - 255 * i / CB; wheel[k][2] = 255; }
+  for (int i = 0; i < BM; ++i, ++k) { wheel[k][0] = 255 * i / BM; wheel[k][1] = 0; wheel[k][2] = 255; }
+  for (int i = 0; i < MR; ++i, ++k) { wheel[k][0] = 255; wheel[k][1] = 0; wheel[k][2] = 255 - 255 * i / MR; }
+  size_t n = (size_t)w * h;
+  float maxrad = maxmotion;                                  /* :89-106 */
+  if (maxmotion <= 0) {
+    maxrad = 1;
+    for (size_t i = 0; i < n; ++i) {
+      float x = flow[2 * i], y = flow[2 * i + 1];
+      if (!flow_ok(x, y)) continue;
+      float r = sqrtf(x * x + y * y);
+      if (r > maxrad) maxrad = r;
+    }
+  }
+  memset(bgr, 0, 3 * n);                                     /* dst.setTo(0), :86 */
+  for (size_t i = 0; i < n; ++i) {
+    float x = flow[2 * i], y = flow[2 * i + 1];
+    if (!flow_ok(x, y)) continue;
+    float fx = x / maxrad, fy = y / maxrad;                  /* :113 */
+    float rad = sqrtf(fx * fx + fy * fy);                    /* :55-60 */
+    float a = atan2f(-fy, -fx) / (float)3.1415926535897932384626433832795;
+    float fk = (a + 1.0f) / 2.0f * (NCOLS - 1);
+    int k0 = (int)fk;
+    int k1 = (k0 + 1) % NCOLS;
+    float f = fk - k0;
+    for (int b = 0; b < 3; ++b) {                            /* :64-78 */
+      float col0 = wheel[k0][b] / 255.f;
+      float col1 = wheel[k1][b] / 255.f;
+      float col = (1 - f) * col0 + f * col1;
+      if (rad <= 1) col = 1 - rad * (1 - col);
+      else col *= .75f;
+      bgr[3 * i + (2 - b)] = (uint8_t)(255.f * col);
+    }
+  }
+}

@@ -148,3 +148,20 @@ def test_finest_scale_epilogue(oracle_port):
         assert np.abs(out - exp).max() < 1e-5
     finally:
         e.close()
+
+
+def test_colour_coding_matches_oracle(eng, oracle_port):
+    """dis_color_code == draw_optical_flow (/root/reference/src/color_coding.cpp:83-117), byte for byte:
+    automatic range (maxmotion <= 0), fixed range, invalid vectors, and the device-resident variant."""
+    a, b, _ = dis_b200.synth.make_pair(256, 112, seed=9)
+    flow = eng.run_pair(a, b)
+    ref = oracle_port.color_code(flow)
+    assert np.array_equal(eng.color_code(flow), ref)
+    assert np.array_equal(eng.color_code_pair(0, 112, 256), ref)
+    assert np.array_equal(eng.color_code(flow, 1.5), oracle_port.color_code(flow, 1.5))
+    rng = np.random.default_rng(3)
+    f = (rng.normal(size=(97, 131, 2)) * 4).astype(np.float32)
+    f[0, 0] = np.nan; f[5, 7] = (3e9, 1); f[9, 9] = 0; f[10, 10] = (0, -0.0); f[11, 11] = (-0.0, 0.0)
+    assert np.array_equal(eng.color_code(f), oracle_port.color_code(f))
+    z = np.zeros((8, 8, 2), np.float32)
+    assert (eng.color_code(z) == 255).all()

@@ -84,6 +84,8 @@ def test_ragged_sizes(eng, oracle_port, w, h, seed):
     dict(patch_size=16, patch_overlap=0.8, coarsest_scale=2),
     dict(patch_norm=0),
     dict(max_iter=0), dict(max_iter=1), dict(max_iter=7), dict(max_iter=100),
+    dict(max_iter=22), dict(max_iter=23), dict(max_iter=24), dict(max_iter=25),   # around the hand-off between the two search phases
+    dict(max_iter=24, patch_size=12, patch_overlap=0.75, coarsest_scale=2),
     dict(patch_overlap=0.0), dict(patch_overlap=0.95),           # steps = 8 (no overlap) / steps = 1
     dict(coarsest_scale=0), dict(coarsest_scale=1), dict(coarsest_scale=4),
 ])

@@ -130,3 +130,17 @@ def test_flat_patch_keeps_init(oracle_port):
     flow, d = oracle_port.run_pair_u8(a, a, dump=True, iterations=5)
     assert not flow.any()
     assert all((it == 6).all() for it in d["iters"])
+
+
+def test_colour_coding_known_answers(oracle_port):
+    """compute_color (/root/reference/src/color_coding.cpp:13-81): zero flow is white, unit flow along +x
+    is wheel entry 0 (pure red, stored B,G,R), invalid vectors stay black, range > 1 is dimmed by 0.75."""
+    f = np.zeros((2, 4, 2), np.float32)
+    f[0, 1] = (1, 0); f[0, 2] = (np.nan, 0); f[0, 3] = (2e9, 0); f[1, 0] = (-1, 0); f[1, 1] = (0, 1)
+    c = oracle_port.color_code(f)
+    assert c[0, 0].tolist() == [255, 255, 255]
+    assert c[0, 1].tolist() == [0, 0, 255]
+    assert c[0, 2].tolist() == [0, 0, 0] and c[0, 3].tolist() == [0, 0, 0]
+    assert c[1, 0].tolist() == [255, 255, 0] or c[1, 0][2] == 0          # opposite direction: cyan side of the wheel
+    d = oracle_port.color_code(f, maxmotion=0.5)                          # radius 2 > 1: colour * 0.75
+    assert d[0, 1].tolist() == [0, 0, 191]
