@@ -196,9 +196,11 @@ def main():
     dev_ms = eng.timer_stop_ms()
     barrier()
     dev_ms = max_over_ranks(dev_ms)
-    # per-launch duration of the dominant kernel, measured live (events around each launch, last step)
+    # per-launch durations of the three search kernels, measured live (events around each launch, last step)
     search_ms, n_search = eng.last_search_ms()
-    lvl_ms = [eng.last_search_level_ms(l) for l in range(eng.num_levels())]
+    nl = eng.num_levels()
+    lvl_ms = [eng.last_search_level_ms(l) for l in range(nl)]
+    phase_ms = [[eng.last_search_phase_ms(l, ph) for l in range(nl)] for ph in range(3)]
     st = eng.stats()
     launches_per_step = st["kernel_launches"]
 
@@ -218,17 +220,28 @@ def main():
     clocks = sampler.stop() if sampler else None
     checksum = float(np.abs(pin_out.numpy()).mean())
 
+    # run counters summed over ranks (NCCL all-reduce; statistics only — no pixel data crosses ranks)
+    job = dis_b200.parallel.reduce_stats(st, dev_ms, dist, "cuda")
     if rank == 0:
         hbm_peak, sm_max, peak_src = measured_peaks()
         value = world * N_PAIRS * args.steps / (dev_ms * 1e-3)
         e2e = world * N_PAIRS * args.steps / e2e_s
-        # algorithmic bytes of one step's inverse-search launches: the three live planes per level
-        # (first.dx, first.dy, second.img; padded sizes), the coarser flow read and the patch flows written
-        alg = 0
-        for l in range(eng.num_levels()):
-            li = eng.level_info(l)
-            alg += N_PAIRS * (3 * 4 * li["tmp_w"] * li["tmp_h"] + 8 * li["num_patches"] + (8 * (li["width"] // 2) * (li["height"] // 2) if l < eng.num_levels() - 1 else 0))
-        achieved = alg / (search_ms * 1e-3) / 1e9
+        # Algorithmic HBM bytes per launch, summed over the 4 levels of a step:
+        #  k_converge: the three live padded planes (first.dx, first.dy, second.img), the coarser flow read,
+        #              the 288-byte hand-off record written per patch;
+        #  walk:       the hand-off record read, u (8 B) and the iteration count (4 B) written per patch.
+        infos = [eng.level_info(l) for l in range(nl)]
+        patches = sum(li["num_patches"] for li in infos) * N_PAIRS
+        alg_conv = sum(N_PAIRS * (3 * 4 * li["tmp_w"] * li["tmp_h"] + 288 * li["num_patches"]
+                                  + (8 * (li["width"] // 2) * (li["height"] // 2) if l < nl - 1 else 0)) for l, li in enumerate(infos))
+        alg_walk = 300 * patches
+        conv_ms, walk_ms, strag_ms = (sum(x) for x in phase_ms)
+        achieved = alg_walk / (walk_ms * 1e-3) / 1e9
+        alg = alg_conv + alg_walk
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "r1_walk_traffic.json")   # dram bytes of the walk launches, one ncu --set full capture
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get("dram_bytes_per_step")
         sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
         issue_peak = 148 * 128 * sm_mhz * 1e6           # fp32 lane-ops/s without FMA at the measured clock
         it_rate = st["patch_iterations"] / (search_ms * 1e-3)
@@ -244,16 +257,23 @@ def main():
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(pin_in.numel()), "d2h_bytes_per_step": int(pin_out.numel() * 4),
                     "api": "dis_run_sequence_u8 (pinned host buffers)", "ms_per_step": 1e3 * e2e_s / args.steps},
             "gpu_launches": int(launches_per_step * args.steps),
-            "roofline": {"kernel": "k_inverse_search<8,4> (4 launches per step, one per level)", "bound": "hbm",
-                         "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
-                         "peak_source": peak_src, "algorithmic_bytes_per_step": alg, "kernel_ms_per_step": search_ms,
-                         "kernel_ms_per_level_fine_to_coarse": lvl_ms,
-                         "note": "latency/issue-bound, not HBM-bound (SURVEY.md §8d): see roofline_issue"},
+            "roofline": {"kernel": "k_inverse_search<8,8> = the memoised walk (4 launches per step, one per level; figures are per step)",
+                         "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "traffic": traffic, "peak_source": peak_src + " (burst figure of MEASURED_PEAKS.json)",
+                         "algorithmic_bytes_per_step": alg_walk, "kernel_ms_per_step": walk_ms,
+                         "kernel_ms_per_level_fine_to_coarse": phase_ms[1],
+                         "note": "issue/latency-bound, not HBM-bound (SURVEY.md §8d, DESIGN.md §3.2): see roofline_issue"},
+            "roofline_kernels": [
+                {"kernel": "k_converge<8,4>", "ms_per_step": conv_ms, "algorithmic_bytes_per_step": alg_conv,
+                 "achieved_gbs": alg_conv / (conv_ms * 1e-3) / 1e9, "frac_hbm": alg_conv / (conv_ms * 1e-3) / 1e9 / hbm_peak,
+                 "fp32_lane_ops_per_s": min(24, args.max_iter + 1) * patches * F_ITER / (conv_ms * 1e-3),
+                 "ms_per_level_fine_to_coarse": phase_ms[0]},
+                {"kernel": "k_stragglers<8,4>", "ms_per_step": strag_ms, "ms_per_level_fine_to_coarse": phase_ms[2]}],
             "roofline_issue": {"unit": "fp32 lane-op/s (no FMA)", "peak": issue_peak, "sm_mhz": sm_mhz,
                                "reference_equivalent": {"patch_iterations_per_s": it_rate, "frac": it_rate * F_ITER / issue_peak},
                                "executed": {"sampled_iterations_per_s": smp_rate, "frac": smp_rate * F_ITER / issue_peak},
                                "tap_bytes_per_s_executed": smp_rate * B_TAP},
-            "stats_per_step": st, "search_share_of_step": search_ms / (dev_ms / args.steps),
+            "stats_per_step": st, "stats_job_per_step": job, "search_share_of_step": search_ms / (dev_ms / args.steps),
             "clocks": clocks, "checksum": checksum,
         }
         if world == 1 and not args.no_cpu_baseline:

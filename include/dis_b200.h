@@ -145,6 +145,9 @@ DIS_API int dis_timer_stop_ms(dis_engine* e, float* ms);
 DIS_API int dis_last_search_ms(dis_engine* e, float* ms, int* launches);
 /* Same, for the launch of one level (level = scale - finest_scale). */
 DIS_API int dis_last_search_level_ms(dis_engine* e, int level, float* ms);
+/* Same, for one of the three kernels of a level: phase 0 = k_converge (passes 0..23, every pass
+ * sampled), 1 = k_inverse_search (the memoised walk), 2 = k_stragglers. */
+DIS_API int dis_last_search_phase_ms(dis_engine* e, int level, int phase, float* ms);
 
 /* ---- introspection for the parity harness ---------------------------------------------------
  * Valid after any run; `pair` indexes the pairs of that run, `level` = scale - finest_scale. */

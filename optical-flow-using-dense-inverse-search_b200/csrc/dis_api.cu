@@ -68,7 +68,7 @@ struct dis_engine {
   std::vector<cudaEvent_t> gdone;
   cudaEvent_t fork_ev = nullptr;
   int n_groups = 1;                     // groups of the last run
-  std::vector<cudaEvent_t> search_ev;   // [group][level] pairs of events around each search launch
+  std::vector<cudaEvent_t> search_ev;   // [group][level][4]: before k_converge | before the walk | before k_stragglers | after
   int search_launches = 0;              // per group
   size_t straggler_stride = 0;          // bytes per group in `stragglers`
 
@@ -228,11 +228,9 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
     a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
     a.out2max = sq_threshold(e->outlier);
     a.conv_eps2 = p.conv_eps * p.conv_eps;
-    cudaEvent_t* ev = &e->search_ev[2 * (g * nl + launch)];
-    CU(cudaEventRecord(ev[0], st));
-    const int n = dis::launch_inverse_search(a, p.patch_size, st);
+    cudaEvent_t* ev = &e->search_ev[4 * (g * nl + launch)];
+    const int n = dis::launch_inverse_search(a, p.patch_size, st, ev);
     if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
-    CU(cudaEventRecord(ev[1], st));
     e->launches += n;
     dis::DensifyArgs d;
     d.u = a.u_out; d.dense = L.flow.as<float>() + L.flow_stride * p0; d.dense_stride = L.flow_stride;
@@ -247,7 +245,7 @@ int run_levels(dis_engine* e) {
   const int nl = (int)e->levels.size();
   CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
   const int G = std::max(1, std::min(std::min(kMaxGroups, e->max_groups), e->n_pairs));
-  while ((int)e->search_ev.size() < 2 * nl * G) {
+  while ((int)e->search_ev.size() < 4 * nl * G) {
     cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev);
   }
   while ((int)e->gstream.size() < G - 1) {
@@ -467,7 +465,23 @@ int dis_last_search_level_ms(dis_engine* e, int level, float* ms) {
   *ms = 0.f;
   for (int g = 0; g < e->n_groups; ++g) {   // groups run concurrently: this is the sum of their device times
     float t = 0.f;
-    CU(cudaEventElapsedTime(&t, e->search_ev[2 * (g * nl + i)], e->search_ev[2 * (g * nl + i) + 1]));
+    CU(cudaEventElapsedTime(&t, e->search_ev[4 * (g * nl + i)], e->search_ev[4 * (g * nl + i) + 3]));
+    *ms += t;
+  }
+  return DIS_OK;
+}
+
+int dis_last_search_phase_ms(dis_engine* e, int level, int phase, float* ms) {
+  if (!e || !ms) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->have_run) return fail(DIS_ERR_STATE, "no run yet");
+  const int nl = (int)e->levels.size();
+  if (level < 0 || level >= nl || e->search_launches != nl || phase < 0 || phase > 2) return fail(DIS_ERR_PARAM, "level or phase out of range");
+  CU(cudaStreamSynchronize(e->stream));
+  const int i = nl - 1 - level;
+  *ms = 0.f;
+  for (int g = 0; g < e->n_groups; ++g) {
+    float t = 0.f;
+    CU(cudaEventElapsedTime(&t, e->search_ev[4 * (g * nl + i) + phase], e->search_ev[4 * (g * nl + i) + phase + 1]));
     *ms += t;
   }
   return DIS_OK;
@@ -480,7 +494,7 @@ int dis_last_search_ms(dis_engine* e, float* ms, int* launches) {
   float total = 0.f;
   for (int i = 0; i < e->search_launches * e->n_groups; ++i) {
     float t = 0.f;
-    CU(cudaEventElapsedTime(&t, e->search_ev[2 * i], e->search_ev[2 * i + 1]));
+    CU(cudaEventElapsedTime(&t, e->search_ev[4 * i], e->search_ev[4 * i + 3]));
     total += t;
   }
   *ms = total;

@@ -62,7 +62,8 @@ constexpr int kWalkSeeds = 16;
 constexpr size_t kWalkBytesPerPatch = 32 + 16 * kWalkSeeds;   // walk_state + walk_seeds
 
 // host-callable launchers (each returns the number of kernels launched)
-int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s);
+// ev: optional 4 events recorded before k_converge, before the walk, before k_stragglers and after it
+int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev = nullptr);
 int launch_densify(const DensifyArgs& a, cudaStream_t s);
 
 struct PyramidArgs {

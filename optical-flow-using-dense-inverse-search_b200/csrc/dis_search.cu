@@ -798,7 +798,7 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
 }
 
 template <int PS, int SG, bool FAST>
-int launch_ps(const SearchArgs& a, cudaStream_t s) {
+int launch_ps(const SearchArgs& a, cudaStream_t s, cudaEvent_t* ev) {
   constexpr int WSG = (DIS_WALK_SG8 && PS == 8) ? 8 : SG;   // sub-group size of the walk phase's (rare) service rounds
   const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
   cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -811,21 +811,25 @@ int launch_ps(const SearchArgs& a, cudaStream_t s) {
   int n = 2;
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) cudaMemsetAsync(a.straggler_count, 0, sizeof(int), s);
+  if (ev) cudaEventRecord(ev[0], s);
   {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
     const long long cwant = (total + kConvWarps * Geom<PS, SG>::G - 1) / (kConvWarps * Geom<PS, SG>::G);
     const long long cslots = 148LL * 12 / (a.share > 1 ? a.share : 1);
     k_converge<PS, SG, FAST><<<(unsigned)(cwant < cslots ? cwant : cslots), kConvWarps * 32, 0, s>>>(a);
   }
+  if (ev) cudaEventRecord(ev[1], s);
   k_inverse_search<PS, WSG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
+  if (ev) cudaEventRecord(ev[2], s);
   if (a.stragglers) { k_stragglers<PS, SG, FAST><<<148 * 4, 128, 0, s>>>(a); ++n; }
+  if (ev) cudaEventRecord(ev[3], s);
   return n;
 }
 
 }  // namespace
 
-int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s) {
+int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev) {
   const bool fast = a.conv_eps2 > 0.f;
-#define DIS_CASE(PS, SG) case PS: return fast ? launch_ps<PS, SG, true>(a, s) : launch_ps<PS, SG, false>(a, s);
+#define DIS_CASE(PS, SG) case PS: return fast ? launch_ps<PS, SG, true>(a, s, ev) : launch_ps<PS, SG, false>(a, s, ev);
   switch (patch_size) {
     DIS_CASE(4, 4) DIS_CASE(6, 4) DIS_CASE(8, 4) DIS_CASE(10, 8) DIS_CASE(12, 8) DIS_CASE(16, 8)
     default: return -1;

@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "dis_default_params", "dis_last_error", "dis_version", "dis_create", "dis_destroy", "dis_run_pair_u8",
     "dis_run_batch_u8", "dis_run_sequence_u8", "dis_run_pyramids", "dis_construct_pyramid", "dis_upload_frames_u8",
     "dis_run_resident", "dis_download_flows", "dis_synchronize", "dis_timer_start", "dis_timer_stop_ms",
-    "dis_last_search_ms", "dis_last_search_level_ms", "dis_num_levels", "dis_get_level_info", "dis_get_patches", "dis_get_level_flow",
+    "dis_last_search_ms", "dis_last_search_level_ms", "dis_last_search_phase_ms", "dis_num_levels", "dis_get_level_info", "dis_get_patches", "dis_get_level_flow",
     "dis_get_plane", "dis_get_stats", "dis_grid_create", "dis_grid_create_single", "dis_grid_destroy", "dis_grid_init", "dis_grid_set_target",
     "dis_grid_init_from_prev_flow", "dis_grid_set_patch_init", "dis_grid_inverse_search", "dis_grid_densify",
     "dis_grid_num_patches", "dis_grid_get_patch", "dis_write_flo", "dis_read_flo", "dis_read_flo_size",
@@ -220,6 +220,12 @@ class Engine:
         ms, n = C.c_float(), C.c_int()
         _chk(self.lib.dis_last_search_ms(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def last_search_phase_ms(self, level: int, phase: int) -> float:
+        """Device time of one kernel of a level: 0 k_converge, 1 k_inverse_search (walk), 2 k_stragglers."""
+        ms = C.c_float()
+        _chk(self.lib.dis_last_search_phase_ms(self._h, int(level), int(phase), C.byref(ms)))
+        return ms.value
 
     def last_search_level_ms(self, level: int) -> float:
         ms = C.c_float()
