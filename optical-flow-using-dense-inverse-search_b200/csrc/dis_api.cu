@@ -220,7 +220,7 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
     a.walk_state = e->walk.as<char>() + 32 * (size_t)I.num_patches * p0;
     a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * I.num_patches * p0;
     a.n_pairs = p1 - p0;
-    a.share = e->n_groups;
+    a.share = getenv("DIS_SHARE") ? e->n_groups : 1;   // full-size grids: a later group fills the SMs an earlier group's tail leaves idle
     a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
     a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
     a.warps_per_pair = (I.num_patches + 31) / 32;

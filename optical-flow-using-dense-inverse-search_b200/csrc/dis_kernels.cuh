@@ -58,7 +58,10 @@ struct DensifyArgs {
   int n_pairs, width, height, npw, nph, offw, offh, steps, np, ps;
 };
 
-constexpr int kWalkSeeds = 16;
+#ifndef DIS_SLOTS
+#define DIS_SLOTS 16
+#endif
+constexpr int kWalkSeeds = DIS_SLOTS;   // entries of a patch's {position -> delta_u} cache (16 or 32)
 constexpr size_t kWalkBytesPerPatch = 32 + 16 * kWalkSeeds;   // walk_state + walk_seeds
 
 // host-callable launchers (each returns the number of kernels launched)

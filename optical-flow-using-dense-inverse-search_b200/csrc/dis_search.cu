@@ -41,7 +41,14 @@
 namespace dis {
 namespace {
 
-constexpr int kSlots = 16;            // cache entries per patch
+constexpr int kSlots = kWalkSeeds;    // cache entries per patch: 4 sets (bit 0 of x, bit 0 of y) x kSlots/4 ways
+static_assert(kSlots == 16 || kSlots == 32, "cache geometry");
+constexpr int kWays = kSlots / 4;
+constexpr int kWayBits = kSlots == 32 ? 3 : 2;
+// Slot predicted for a position: low bits of x (2 or 3) above the low 2 bits of y.
+__device__ __forceinline__ int slot_of(unsigned bx, unsigned by) { return ((bx & (kSlots / 4 - 1)) << 2) | (by & 3); }
+// XOR distance, in slot index space, between way 0 and way w of a set (way bit 0 = bit 1 of y, bits 1.. = bits 1.. of x)
+__host__ __device__ constexpr int way_xor(int w) { return ((w & 1) << 1) | ((w >> 1) << 3); }
 #ifndef DIS_CHUNK
 #define DIS_CHUNK 8
 #endif
@@ -294,18 +301,23 @@ __device__ __forceinline__ bool must_reset(float px, float py, float stx, float 
 // FIFO victim way.  DEDUP: skip the insertion when the position is already present in its set.
 template <int STRIDE, bool DEDUP>
 __device__ __forceinline__ void cache_insert(uint4* cache, unsigned& fifo, const uint4 e) {
-  const int p = ((e.x & 3) << 2) | (e.y & 3);
+  const int p = slot_of(e.x, e.y);
   const uint4 old = cache[p * STRIDE];
   if (DEDUP) {
     if (old.x == e.x && old.y == e.y) return;
-    const uint4 e1 = cache[(p ^ 8) * STRIDE], e2 = cache[(p ^ 2) * STRIDE], e3 = cache[(p ^ 10) * STRIDE];
-    if ((e1.x == e.x && e1.y == e.y) || (e2.x == e.x && e2.y == e.y) || (e3.x == e.x && e3.y == e.y)) return;
+    bool found = false;
+#pragma unroll
+    for (int w = 1; w < kWays; ++w) {
+      const uint4 o = cache[(p ^ way_xor(w)) * STRIDE];
+      found = found || (o.x == e.x && o.y == e.y);
+    }
+    if (found) return;
   }
   if (old.x != 0xffffffffu) {
     const int set = ((p >> 1) & 2) | (p & 1);
-    const int way = (fifo >> (2 * set)) & 3;
-    fifo = (fifo & ~(3u << (2 * set))) | (((way + 1) & 3) << (2 * set));
-    const int q = (p & 5) | ((way & 2) << 2) | ((way & 1) << 1);
+    const int way = (fifo >> (kWayBits * set)) & (kWays - 1);
+    fifo = (fifo & ~((unsigned)(kWays - 1) << (kWayBits * set))) | (((way + 1) & (kWays - 1)) << (kWayBits * set));
+    const int q = (p & 5) | way_xor(way);
     if (q != p) cache[q * STRIDE] = old;                      // the displaced entry moves there
   }
   cache[p * STRIDE] = e;
@@ -313,20 +325,27 @@ __device__ __forceinline__ void cache_insert(uint4* cache, unsigned& fifo, const
 
 enum : int { ST_RUN = 0, ST_WAIT = 1, ST_FREE = 3 };
 
-constexpr int kWarps = 8;            // warps per block (independent of one another)
+#ifndef DIS_WARPS
+#define DIS_WARPS (DIS_SLOTS == 32 ? 4 : 8)
+#endif
+constexpr int kWarps = DIS_WARPS;    // warps per block (independent of one another)
 #ifndef DIS_WALK_SG8
 #define DIS_WALK_SG8 1
 #endif
 // Resident blocks per SM of the walk kernel.  ps 8 serves its (rare) misses with 8-lane sub-groups: 8 elements
 // per lane fit 85 registers, so three blocks (24 warps) hide the LDS -> compare -> add chain of the fast loop;
 // the other patch sizes need 128 registers for their service rounds.
-constexpr int walk_blocks(int ps, int sg) { return (ps == 8 && sg == 8) ? 3 : 2; }
+#ifdef DIS_WALK_BLOCKS
+constexpr int walk_blocks(int, int) { return DIS_WALK_BLOCKS; }
+#else
+constexpr int walk_blocks(int ps, int sg) { return (kSlots == 32 || (ps == 8 && sg == 8)) ? 3 : 2; }
+#endif
 constexpr int kStreakLimit = 64;     // consecutive first-seen positions before a patch is handed off
 constexpr int kRebindMin = DIS_REBIND_MIN;       // free lanes a warp gathers before it fetches new patches
 
 // per-warp shared memory
 struct WarpSmem {
-  uint4 cache[kSlots][32];           // per lane: 16 x {bx, by, dx, dy}
+  uint4 cache[kSlots][32];           // per lane: kSlots x {bx, by, dx, dy}
   float4 res[32];                    // service results, per lane
   int list[32];                      // lanes to serve, in rank order
 };
@@ -565,7 +584,7 @@ k_inverse_search(const SearchArgs A) {
 #pragma unroll
     for (int it = 0; it < kChunk; ++it) {
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-      const uint4 e = cache[(((bx & 3) << 2) | (by & 3)) * 32];
+      const uint4 e = cache[slot_of(bx, by) * 32];
       run = run && e.x == bx && e.y == by && k <= iters;
       if (run) {
         ++k;
@@ -583,17 +602,20 @@ k_inverse_search(const SearchArgs A) {
     // ---- lanes that left the fast phase: probe all four ways of the set ---------------------------
     if (state == ST_RUN && !run && !fin) {
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-      const int p = ((bx & 3) << 2) | (by & 3);
-      const uint4 e0 = cache[p * 32], e1 = cache[(p ^ 8) * 32], e2 = cache[(p ^ 2) * 32], e3 = cache[(p ^ 10) * 32];
-      const bool m0 = e0.x == bx && e0.y == by, m1 = e1.x == bx && e1.y == by;
-      const bool m2 = e2.x == bx && e2.y == by, m3 = e3.x == bx && e3.y == by;
-      if (m0 || m1 || m2 || m3) {
+      const int p = slot_of(bx, by);
+      uint4 e = cache[p * 32];
+      bool hit = e.x == bx && e.y == by;
+#pragma unroll
+      for (int w = 1; w < kWays; ++w) {
+        const uint4 o = cache[(p ^ way_xor(w)) * 32];
+        if (o.x == bx && o.y == by) { e = o; hit = true; }
+      }
+      if (hit) {
 #ifdef DIS_DEBUG_STATS
         atomicAdd(&A.counters[9], 1ull);
 #endif
         if (k > iters) fin = true;                          // src/patch.cpp:199-201 (position already vetted)
         else {
-          const uint4 e = m0 ? e0 : m1 ? e1 : m2 ? e2 : e3;
           ++k;
           const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
           ux = ux - dx; uy = uy - dy;
