@@ -226,7 +226,7 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
     a.warps_per_pair = (I.num_patches + 31) / 32;
     a.iterations = p.max_iter; a.patnorm = p.patch_norm ? 1 : 0;
     a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
-    a.out2max = sq_threshold(e->outlier);
+    a.out2max = sq_threshold(e->outlier); a.tile_margin = (int)ceilf(e->outlier) + 1;
     a.conv_eps2 = p.conv_eps * p.conv_eps;
     cudaEvent_t* ev = &e->search_ev[4 * (g * nl + launch)];
     const int n = dis::launch_inverse_search(a, p.patch_size, st, ev);
@@ -893,7 +893,7 @@ int dis_grid_inverse_search(dis_grid* g) {
   a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
   a.warps_per_pair = (I.num_patches + 31) / 32;
   a.iterations = e->prm.max_iter; a.patnorm = e->prm.patch_norm ? 1 : 0;
-  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.out2max = sq_threshold(e->outlier);
+  a.lb = g->lb; a.ub_w = g->ub_w; a.ub_h = g->ub_h; a.out2max = sq_threshold(e->outlier); a.tile_margin = (int)ceilf(e->outlier) + 1;
   a.conv_eps2 = e->prm.conv_eps * e->prm.conv_eps;
   if (dis::launch_inverse_search(a, e->prm.patch_size, e->stream) < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
   CU(cudaGetLastError());

@@ -49,6 +49,8 @@ struct SearchArgs {
   float lb, ub_w, ub_h;
   float out2max;            // largest fp32 s with sqrtf(s) <= outlierthresh: |start-pos| > thr <=> s > out2max
   float conv_eps2;          // conv_eps^2; 0 = off (reference behaviour)
+  int handoff_misses;       // walk -> k_stragglers after this many misses of a patch (set by the launcher from the launch size)
+  int tile_margin;          // ceil(outlierthresh) + 1: how far (px) a tap base can move from the start position's before a reset
 };
 
 struct DensifyArgs {

@@ -34,6 +34,7 @@
 //     window in registers, 32/SG per warp.
 //  (tools/micro/ keeps the measured alternatives: single-kernel designs with tile-bound warps, and
 //  warp-specialised walker/sampler blocks with a shared-memory request queue; DESIGN.md has the numbers.)
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "dis_kernels.cuh"
@@ -54,6 +55,18 @@ __host__ __device__ constexpr int way_xor(int w) { return ((w & 1) << 1) | ((w >
 #endif
 #ifndef DIS_AGE
 #define DIS_AGE 4
+#endif
+#ifndef DIS_HEAVY
+#define DIS_HEAVY 100000
+#endif
+#ifndef DIS_EARLY
+#define DIS_EARLY 0
+#endif
+#ifndef DIS_STRAG_SG8
+#define DIS_STRAG_SG8 0
+#endif
+#ifndef DIS_STRAG_BLOCKS
+#define DIS_STRAG_BLOCKS 4
 #endif
 #ifndef DIS_N1
 #define DIS_N1 24
@@ -260,6 +273,14 @@ struct Window8 {
   static constexpr int H = 8 / SG;
   float t0[H][9], t1[H][9];
   int bx, by;                                  // the (clamped) tap base the registers hold; -1: nothing loaded
+  // same taps from a shared-memory tile; w0 = address of tap (bxi - 5, byi - 5), rows `stride` floats apart
+  __device__ __forceinline__ void load_tile(const float* w0, int stride, int sl, int bxi, int byi) {
+    bx = bxi; by = byi;
+#pragma unroll
+    for (int h = 0; h < H; ++h)
+#pragma unroll
+      for (int r = 0; r < 9; ++r) { t0[h][r] = w0[r * stride + sl + 4 * h]; t1[h][r] = w0[r * stride + sl + 4 * h + 1]; }
+  }
   __device__ __forceinline__ void load(const float* __restrict__ imB, int tw, int sl, int bxi, int byi) {
     bx = bxi; by = byi;
 #pragma unroll
@@ -380,9 +401,15 @@ __device__ __forceinline__ float2 patch_init(const SearchArgs& A, int idx, int p
 // gradients, LU factors and (ps 8) the tap window stay in registers, a pass is pure fp32 arithmetic.
 // Patches that end here (start out of bounds, reset, max_iter < kN1, conv_eps) are written out;
 // the others leave {u, k, LU} and their last kSeed {position -> delta_u} pairs for the walk phase.
-constexpr int kConvWarps = 4;
+#ifndef DIS_CONV_WARPS
+#define DIS_CONV_WARPS 8
+#endif
+#ifndef DIS_CONV_BLOCKS
+#define DIS_CONV_BLOCKS 2
+#endif
+constexpr int kConvWarps = DIS_CONV_WARPS;
 template <int PS, int SG, bool FAST>
-__global__ void __launch_bounds__(kConvWarps * 32) k_converge(const SearchArgs A) {
+__global__ void __launch_bounds__(kConvWarps * 32, DIS_CONV_BLOCKS) k_converge(const SearchArgs A) {
   using G = Geom<PS, SG>;
   const int lane = threadIdx.x & 31, sub = lane / SG, sl = lane % SG;
   const int gwarp = blockIdx.x * kConvWarps + (threadIdx.x >> 5);
@@ -520,7 +547,7 @@ k_inverse_search(const SearchArgs A) {
   float refx = 0.f, refy = 0.f, inx = 0.f, iny = 0.f, stx = 0.f, sty = 0.f;
   float ux = 0.f, uy = 0.f, px = 0.f, py = 0.f;
   unsigned fifo = 0;
-  int streak = 0, k_posted = -2, waited = 0;
+  int streak = 0, k_posted = -2, waited = 0, misses = 0;
   bool was_reset = false;
   LU2 lu;
   lu.p = lu.q = lu.l = lu.u11 = 0.f; lu.swap = false;
@@ -561,7 +588,7 @@ k_inverse_search(const SearchArgs A) {
             lu.p = w1.x; lu.q = w1.y; lu.l = w1.z; lu.u11 = w1.w;
             lu.swap = (__float_as_int(w0.w) & 1) != 0;
             fifo = (unsigned)__float_as_int(w0.w) >> 8;
-            streak = 0; k_posted = -2; was_reset = false; waited = 0;
+            streak = 0; k_posted = -2; was_reset = false; waited = 0; misses = 0;
             const uint4* __restrict__ seed = reinterpret_cast<const uint4*>(A.walk_seeds) + (size_t)idx * kSlots;
 #pragma unroll
             for (int s = 0; s < kSlots; ++s) cache[s * 32] = __ldg(seed + s);   // the cache image k_converge built
@@ -583,6 +610,7 @@ k_inverse_search(const SearchArgs A) {
 #endif
 #pragma unroll
     for (int it = 0; it < kChunk; ++it) {
+      if (DIS_EARLY && it == DIS_EARLY && !__any_sync(kFull, run)) break;
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
       const uint4 e = cache[slot_of(bx, by) * 32];
       run = run && e.x == bx && e.y == by && k <= iters;
@@ -627,7 +655,7 @@ k_inverse_search(const SearchArgs A) {
         streak = (k == k_posted + 1) ? streak + 1 : 1;
         k_posted = k;
         state = ST_WAIT;
-        if (streak >= kStreakLimit && k >= kHandoffMinIter && A.stragglers) {
+        if (((streak >= kStreakLimit && k >= kHandoffMinIter) || misses >= A.handoff_misses) && A.stragglers) {
           // the orbit does not settle: hand the patch to k_stragglers
           if (must_reset(px, py, stx, sty, A)) { ux = inx; uy = iny; was_reset = true; fin = true; }
           else if (k > iters) fin = true;
@@ -653,7 +681,7 @@ k_inverse_search(const SearchArgs A) {
       const int nwait = __popc(wait_mask);
       const int rem = nwait % G::G;
       const bool others = __ballot_sync(kFull, state == ST_RUN && !fin) != 0;
-      const bool aged = __any_sync(kFull, needs && waited >= DIS_AGE);
+      const bool aged = __any_sync(kFull, needs && (waited >= DIS_AGE || misses >= DIS_HEAVY));   // frequent missers are not made to wait
       const int nserv = (!others || 2 * rem >= G::G || aged) ? nwait : nwait - rem;
       const int rank = __popc(wait_mask & ((1u << lane) - 1u));
       served = needs && rank < nserv;
@@ -690,7 +718,7 @@ k_inverse_search(const SearchArgs A) {
       } else {
         const float2 d = lu.solve(g.x, g.y);                 // src/patch.cpp:176
         cache_insert<32, false>(cache, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y)));
-        ++c_sampled;
+        ++c_sampled; ++misses;
         ++k;
         ux = ux - d.x; uy = uy - d.y;
         px = refx + ux; py = refy + uy;
@@ -726,9 +754,18 @@ k_inverse_search(const SearchArgs A) {
 
 // Patches handed off by k_inverse_search: every pass samples, one patch per sub-group with its
 // template gradients in registers.  Same arithmetic, same order of tests.
+// Everything a straggler can touch lies within outlierthresh of its start position (beyond it the patch is
+// reset, src/patch.cpp:185), so ps 8 stages that neighbourhood of the second image — kTile x kTile taps
+// around the start — in shared memory once per patch: the ~950-pass chain then never waits on L2.
+constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
+constexpr int kStragWarps = 4;
 template <int PS, int SG, bool FAST>
-__global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
+__global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArgs A) {
   using G = Geom<PS, SG>;
+  extern __shared__ float tiles[];
+  const int th = A.height + 2 * A.pad;
+  const bool use_tile = PS == 8 && A.tile_margin <= kTileMargin && A.tmp_w >= kTile && th >= kTile;
+  float* tile = tiles + ((threadIdx.x >> 5) * G::G + (threadIdx.x & 31) / SG) * (kTile * kTileStride);
   const int lane = threadIdx.x & 31, sub = lane / SG, sl = lane % SG;
   const int gwarp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int nwarps = gridDim.x * (blockDim.x >> 5);
@@ -776,12 +813,29 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
     unsigned was_reset = 0, ns = 0;
     Window8<SG> Wn;
     Wn.bx = -1; Wn.by = -1;
+    int ox = 0, oy = 0;
+    if (PS == 8 && use_tile) {
+      const int2 tb0 = tap_base<PS>(stx, sty, A.pad, wmax, hmax);
+      ox = min(max(tb0.x - 5 - kTileMargin, 0), tw - kTile);
+      oy = min(max(tb0.y - 5 - kTileMargin, 0), th - kTile);
+      __syncwarp();
+      for (int i = sl; i < kTile * kTile; i += SG) {
+        const int r = i / kTile, c = i - r * kTile;
+        tile[r * kTileStride + c] = __ldg(imB + (oy + r) * tw + ox + c);
+      }
+      __syncwarp();
+    }
 #pragma unroll 1
     while (__any_sync(kFull, active)) {
       float2 sg;
       if constexpr (PS == 8) {                               // tap window in registers, reloaded when the base moves
         const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
-        if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) Wn.load(imB, tw, sl, tb.x, tb.y);
+        if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) {
+          if (use_tile) {   // a base outside the tile belongs to a position the reset test rejects: clamp, result unused
+            const int rx = min(max(tb.x - 5 - ox, 0), kTile - 9), ry = min(max(tb.y - 5 - oy, 0), kTile - 9);
+            Wn.load_tile(tile + ry * kTileStride + rx, kTileStride, sl, tb.x, tb.y);
+          } else Wn.load(imB, tw, sl, tb.x, tb.y);
+        }
         sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
@@ -820,7 +874,8 @@ __global__ void __launch_bounds__(128) k_stragglers(const SearchArgs A) {
 }
 
 template <int PS, int SG, bool FAST>
-int launch_ps(const SearchArgs& a, cudaStream_t s, cudaEvent_t* ev) {
+int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev) {
+  SearchArgs a = a_in;
   constexpr int WSG = (DIS_WALK_SG8 && PS == 8) ? 8 : SG;   // sub-group size of the walk phase's (rare) service rounds
   const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
   cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -831,18 +886,35 @@ int launch_ps(const SearchArgs& a, cudaStream_t s, cudaEvent_t* ev) {
   const long long slots = (148 * walk_blocks(PS, WSG) + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
   const unsigned blocks = (unsigned)(want < slots ? want : slots);
   int n = 2;
+  {   // Small launches are bound by the serial miss chains of their few restless patches, not by throughput:
+      // hand those to k_stragglers (one pass every ~0.6 us, template and taps on chip) after fewer misses.
+    static const char* env = getenv("DIS_HANDOFF");
+    int t0 = 16, t1 = 32, t2 = 128;
+    if (env) sscanf(env, "%d,%d,%d", &t0, &t1, &t2);
+    a.handoff_misses = total < 200000 ? t0 : total < 600000 ? t1 : total < 2000000 ? t2 : (1 << 30);
+  }
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) cudaMemsetAsync(a.straggler_count, 0, sizeof(int), s);
   if (ev) cudaEventRecord(ev[0], s);
   {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
     const long long cwant = (total + kConvWarps * Geom<PS, SG>::G - 1) / (kConvWarps * Geom<PS, SG>::G);
-    const long long cslots = 148LL * 12 / (a.share > 1 ? a.share : 1);
+    const long long cslots = 148LL * (DIS_CONV_BLOCKS > 1 ? DIS_CONV_BLOCKS * 4 : 12) / (a.share > 1 ? a.share : 1);
+    // one shared-memory carve-out for all three kernels: kernels with different carve-outs cannot share an SM,
+    // which would keep concurrent pair groups from filling each other's tails
+    cudaFuncSetAttribute(k_converge<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     k_converge<PS, SG, FAST><<<(unsigned)(cwant < cslots ? cwant : cslots), kConvWarps * 32, 0, s>>>(a);
   }
   if (ev) cudaEventRecord(ev[1], s);
   k_inverse_search<PS, WSG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
   if (ev) cudaEventRecord(ev[2], s);
-  if (a.stragglers) { k_stragglers<PS, SG, FAST><<<148 * 4, 128, 0, s>>>(a); ++n; }
+  if (a.stragglers) {
+    constexpr int SSG = (DIS_STRAG_SG8 && PS == 8) ? 8 : SG;   // shorter per-pass chains: the kernel is latency-bound
+    const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SSG>::G * kTile * kTileStride : 0;
+    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
+    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    k_stragglers<PS, SSG, FAST><<<148 * DIS_STRAG_BLOCKS, kStragWarps * 32, tsm, s>>>(a);
+    ++n;
+  }
   if (ev) cudaEventRecord(ev[3], s);
   return n;
 }

@@ -35,6 +35,8 @@ for _ in range(reps):
 ms = e.timer_stop_ms() / reps
 st = e.stats()
 lv = [round(e.last_search_level_ms(l), 2) for l in range(e.num_levels())]
+ph = [[round(e.last_search_phase_ms(l, p), 2) for l in range(e.num_levels())] for p in range(3)]
+print(f"  converge {ph[0]} = {sum(ph[0]):.2f} | walk {ph[1]} = {sum(ph[1]):.2f} | stragglers {ph[2]} = {sum(ph[2]):.2f} ms")
 print(f"{(n_frames - 1) / ms * 1e3:.1f} pairs/s  step {ms:.2f} ms  search levels fine->coarse {lv}  "
       f"samples/patch {st['sampled_iterations'] / st['patches']:.2f}")
 e.close()
