@@ -67,6 +67,7 @@ struct dis_engine {
   std::vector<cudaStream_t> gstream;    // group streams (group 0 runs on `stream` itself)
   std::vector<cudaEvent_t> gdone;
   cudaEvent_t fork_ev = nullptr;
+  dis::SearchSide side = {nullptr, nullptr, nullptr, 0, 0};   // k_stragglers beside the walk (single-group runs)
   int n_groups = 1;                     // groups of the last run
   std::vector<cudaEvent_t> search_ev;   // [group][level][4]: before k_converge | before the walk | before k_stragglers | after
   int search_launches = 0;              // per group
@@ -181,7 +182,7 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
     size_t maxp = 0;
     for (const Level& L : e->levels) maxp = std::max(maxp, (size_t)L.info.num_patches * n_pairs);
     e->straggler_cap = (int)std::min<size_t>(maxp / 8 + 4096, (size_t)1 << 28);
-    e->straggler_stride = (64 + (size_t)e->straggler_cap * 20 + 255) & ~(size_t)255;
+    e->straggler_stride = (64 + (size_t)e->straggler_cap * dis::kStragglerBytes + 255) & ~(size_t)255;
     if (e->stragglers.ensure(kMaxGroups * e->straggler_stride)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stragglers) failed");
     // hand-off between the two phases of a level: 32-byte records first, then the seed entries
     e->walk_patches = (maxp + 7) & ~(size_t)7;
@@ -229,7 +230,7 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
     a.out2max = sq_threshold(e->outlier); a.tile_margin = (int)ceilf(e->outlier) + 1;
     a.conv_eps2 = p.conv_eps * p.conv_eps;
     cudaEvent_t* ev = &e->search_ev[4 * (g * nl + launch)];
-    const int n = dis::launch_inverse_search(a, p.patch_size, st, ev);
+    const int n = dis::launch_inverse_search(a, p.patch_size, st, ev, (e->n_groups == 1 && e->side.stream) ? &e->side : nullptr);
     if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
     e->launches += n;
     dis::DensifyArgs d;
@@ -359,6 +360,18 @@ int dis_create(const dis_params* p, int device, dis_engine** out) {
   e->steps = p->steps > 0 ? p->steps : steps_of(p->patch_size, p->patch_overlap);
   e->outlier = p->outlier_thresh > 0.f ? p->outlier_thresh : (float)p->patch_size / 2;   // src/optical_flow.cpp:34
   if (const char* g = getenv("DIS_GROUPS")) e->max_groups = std::max(1, atoi(g));
+  {
+    const char* sb = getenv("DIS_SIDE_BLOCKS");          // 0 = run k_stragglers after the walk instead of beside it
+    e->side.blocks = sb ? (unsigned)std::max(0, atoi(sb)) : 592u;
+    e->side.reserve = getenv("DIS_SIDE_RESERVE") ? 1 : 0;
+    if (e->side.blocks > 0 &&
+        (cudaStreamCreateWithFlags(&e->side.stream, cudaStreamNonBlocking) != cudaSuccess ||
+         cudaEventCreateWithFlags(&e->side.fork, cudaEventDisableTiming) != cudaSuccess ||
+         cudaEventCreateWithFlags(&e->side.join, cudaEventDisableTiming) != cudaSuccess)) {
+      cudaGetLastError();
+      e->side.stream = nullptr;
+    }
+  }
   memset(&e->stats, 0, sizeof e->stats);
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess) {
@@ -378,6 +391,7 @@ void dis_destroy(dis_engine* e) {
   e->stage.release();
   e->out.release(); e->counters.release();
   for (cudaEvent_t ev : e->search_ev) cudaEventDestroy(ev);
+  if (e->side.stream) { cudaStreamDestroy(e->side.stream); cudaEventDestroy(e->side.fork); cudaEventDestroy(e->side.join); }
   for (cudaEvent_t ev : e->gdone) cudaEventDestroy(ev);
   for (cudaStream_t st : e->gstream) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
   if (e->fork_ev) cudaEventDestroy(e->fork_ev);

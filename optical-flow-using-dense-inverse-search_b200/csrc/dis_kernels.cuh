@@ -35,7 +35,7 @@ struct SearchArgs {
   int* iters_out;           // [pair][np] or nullptr
   unsigned long long* counters;  // [4]: patch_iterations, sampled_iterations, resets, start_oob (or nullptr)
   void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
-  int* straggler_count;     // number of entries (device)
+  int* straggler_count;     // [0] entries appended, [1] entries claimed by k_stragglers, [2] "walk finished" flag (device)
   int* work_counter;        // next patch index of the launch (device; zeroed by the launcher)
   void* walk_state;         // [n_pairs*np] 32-byte hand-off records of the convergence phase
   void* walk_seeds;         // [n_pairs*np][kWalkSeeds] uint4 {pos bits x, y, delta_u x, y}
@@ -63,12 +63,16 @@ struct DensifyArgs {
 #ifndef DIS_SLOTS
 #define DIS_SLOTS 16
 #endif
+constexpr int kStragglerBytes = 32;      // one entry of the walk -> k_stragglers hand-off list
 constexpr int kWalkSeeds = DIS_SLOTS;   // entries of a patch's {position -> delta_u} cache (16 or 32)
 constexpr size_t kWalkBytesPerPatch = 32 + 16 * kWalkSeeds;   // walk_state + walk_seeds
 
 // host-callable launchers (each returns the number of kernels launched)
-// ev: optional 4 events recorded before k_converge, before the walk, before k_stragglers and after it
-int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev = nullptr);
+// Optional second stream on which k_stragglers runs CONCURRENTLY with the walk (fork/join: timing-disabled events).
+struct SearchSide { cudaStream_t stream; cudaEvent_t fork, join; unsigned blocks; int reserve; };
+// ev: optional 4 events recorded before k_converge, before the walk, after the walk and after k_stragglers has joined
+int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev = nullptr,
+                          const SearchSide* side = nullptr);
 int launch_densify(const DensifyArgs& a, cudaStream_t s);
 
 struct PyramidArgs {

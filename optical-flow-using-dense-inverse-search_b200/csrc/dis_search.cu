@@ -120,7 +120,12 @@ __device__ __forceinline__ float tree_sum(const float (&v)[Geom<PS, SG>::NPL]) {
   return acc;
 }
 
-struct Straggler { int pair, pid, k; float ux, uy; };
+// Hand-off record walk -> k_stragglers, 32 bytes.  k doubles as the "published" marker: the list is cleared to
+// 0xff (k = -1) before a launch and k is stored last, after a fence, because k_stragglers may run CONCURRENTLY
+// with the walk and consume entries as they appear.
+struct Straggler { int pair, pid; float ux, uy; int k; int pad[3]; };
+static_assert(sizeof(Straggler) == kStragglerBytes, "hand-off list layout");
+__device__ __forceinline__ int ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
 
 // Hand-off record between the two phases of a level (k_converge -> k_inverse_search), 32 bytes.
 // k < 0: the patch finished in the first phase (its u is already in u_out).
@@ -662,8 +667,10 @@ k_inverse_search(const SearchArgs A) {
           else {
             const int slot = atomicAdd(A.straggler_count, 1);
             if (slot < A.straggler_cap) {
-              Straggler s; s.pair = pair; s.pid = idx - pair * A.np; s.k = k; s.ux = ux; s.uy = uy;
-              reinterpret_cast<Straggler*>(A.stragglers)[slot] = s;
+              Straggler* rec = reinterpret_cast<Straggler*>(A.stragglers) + slot;
+              *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(pair), __int_as_float(idx - pair * A.np), ux, uy);
+              __threadfence();
+              *reinterpret_cast<volatile int*>(&rec->k) = k;     // publish
               state = ST_FREE;     // results and counters come from k_stragglers
             } else { atomicSub(A.straggler_count, 1); streak = 0; }
           }
@@ -767,20 +774,52 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
   const bool use_tile = PS == 8 && A.tile_margin <= kTileMargin && A.tmp_w >= kTile && th >= kTile;
   float* tile = tiles + ((threadIdx.x >> 5) * G::G + (threadIdx.x & 31) / SG) * (kTile * kTileStride);
   const int lane = threadIdx.x & 31, sub = lane / SG, sl = lane % SG;
-  const int gwarp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int nwarps = gridDim.x * (blockDim.x >> 5);
-  const int count = min(*A.straggler_count, A.straggler_cap);
   const Straggler* list = reinterpret_cast<const Straggler*>(A.stragglers);
+  int* const ctl = A.straggler_count;                        // [0] appended, [1] claimed, [2] walk finished
   const int tw = A.tmp_w;
   const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
   int eoff[G::NPL];
   element_offsets<PS, SG>(sl, tw, eoff);
   unsigned long long it_total = 0;
   unsigned ns_total = 0, nr_total = 0;
+  const long long t_start = clock64();
 #pragma unroll 1
-  for (int base = gwarp * G::G; base < count; base += nwarps * G::G) {
-    const bool have = base + sub < count;
-    const Straggler e = list[have ? base + sub : base];
+  for (;;) {
+    // ---- claim the next batch of G entries.  The kernel may run concurrently with the walk (ctl[2] == 0):
+    //      entries are then consumed as they are published; a claimed slot that is still empty is waited for
+    //      until the walk has finished, after which ctl[0] is final. ------------------------------------------
+    int base = -1;
+    if (lane == 0) {
+      for (;;) {
+        const int done = ld_volatile(ctl + 2);
+        const int cnt = min(ld_volatile(ctl), A.straggler_cap);
+        if (ld_volatile(ctl + 1) < cnt) { base = atomicAdd(ctl + 1, G::G); break; }
+        if (done) break;                                     // nothing left and nothing more to come
+        __nanosleep(400);
+        if (clock64() - t_start > 20000000000ll) break;      // safety net (~10 s): never spin forever
+      }
+    }
+    base = __shfl_sync(kFull, base, 0);
+    if (base < 0) break;
+    bool have = false;
+    if (sl == 0) {
+      for (;;) {
+        if (ld_volatile(&list[base + sub < A.straggler_cap ? base + sub : 0].k) >= 0 && base + sub < A.straggler_cap) { have = true; break; }
+        if (ld_volatile(ctl + 2) && base + sub >= min(ld_volatile(ctl), A.straggler_cap)) break;   // walk finished: the slot stays empty
+        __nanosleep(200);
+        if (clock64() - t_start > 20000000000ll) break;
+      }
+      __threadfence();
+    }
+    have = __shfl_sync(kFull, have ? 1 : 0, sub * SG) != 0;
+    if (!__any_sync(kFull, have)) continue;
+    Straggler e;
+    {
+      const int src = __shfl_sync(kFull, have ? base + sub : -1, __ffs(__ballot_sync(kFull, have)) - 1);   // a valid entry for idle sub-groups
+      const Straggler* rec = list + (have ? base + sub : src);
+      const float4 f = __ldcg(reinterpret_cast<const float4*>(rec));
+      e.pair = __float_as_int(f.x); e.pid = __float_as_int(f.y); e.ux = f.z; e.uy = f.w; e.k = ld_volatile(&rec->k);
+    }
     const int2 fr = A.pairs[e.pair];
     const float2* __restrict__ gxyA =
         reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
@@ -874,7 +913,7 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
 }
 
 template <int PS, int SG, bool FAST>
-int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev) {
+int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const SearchSide* side) {
   SearchArgs a = a_in;
   constexpr int WSG = (DIS_WALK_SG8 && PS == 8) ? 8 : SG;   // sub-group size of the walk phase's (rare) service rounds
   const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
@@ -889,30 +928,54 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev) {
   {   // Small launches are bound by the serial miss chains of their few restless patches, not by throughput:
       // hand those to k_stragglers (one pass every ~0.6 us, template and taps on chip) after fewer misses.
     static const char* env = getenv("DIS_HANDOFF");
-    int t0 = 16, t1 = 32, t2 = 128;
-    if (env) sscanf(env, "%d,%d,%d", &t0, &t1, &t2);
-    a.handoff_misses = total < 200000 ? t0 : total < 600000 ? t1 : total < 2000000 ? t2 : (1 << 30);
+    int t0 = 24, t1 = 48, t2 = 128, t3 = 384;
+    if (env) sscanf(env, "%d,%d,%d,%d", &t0, &t1, &t2, &t3);
+    a.handoff_misses = total < 200000 ? t0 : total < 600000 ? t1 : total < 2000000 ? t2 : t3;
   }
+  constexpr int SSG = (DIS_STRAG_SG8 && PS == 8) ? 8 : SG;
+  const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SSG>::G * kTile * kTileStride : 0;
+  const bool overlap = a.stragglers && side && side->stream;   // k_stragglers runs beside the walk and eats its hand-offs as they come
+  unsigned walk_grid = blocks;
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
-  if (a.stragglers) cudaMemsetAsync(a.straggler_count, 0, sizeof(int), s);
+  if (a.stragglers) {
+    const long long cap = total / 4 + 64 < a.straggler_cap ? total / 4 + 64 : a.straggler_cap;
+    a.straggler_cap = (int)cap;
+    cudaMemsetAsync(a.straggler_count, 0, 4 * sizeof(int), s);
+    cudaMemsetAsync(a.stragglers, 0xff, (size_t)cap * kStragglerBytes, s);
+    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
+    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  }
   if (ev) cudaEventRecord(ev[0], s);
   {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
     const long long cwant = (total + kConvWarps * Geom<PS, SG>::G - 1) / (kConvWarps * Geom<PS, SG>::G);
     const long long cslots = 148LL * (DIS_CONV_BLOCKS > 1 ? DIS_CONV_BLOCKS * 4 : 12) / (a.share > 1 ? a.share : 1);
-    // one shared-memory carve-out for all three kernels: kernels with different carve-outs cannot share an SM,
-    // which would keep concurrent pair groups from filling each other's tails
+    // one shared-memory carve-out for all three kernels: kernels with different carve-outs cannot share an SM
     cudaFuncSetAttribute(k_converge<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     k_converge<PS, SG, FAST><<<(unsigned)(cwant < cslots ? cwant : cslots), kConvWarps * 32, 0, s>>>(a);
   }
   if (ev) cudaEventRecord(ev[1], s);
-  k_inverse_search<PS, WSG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
+  if (overlap) cudaEventRecord(side->fork, s);               // "convergence phase done"
+  if (overlap && side->reserve) {
+    // k_stragglers starts with the walk: its blocks (4 warps, ~150 registers) take one of the three block slots of
+    // `side->blocks` SMs, the walk gets the rest of the machine.
+    cudaStreamWaitEvent(side->stream, side->fork, 0);
+    k_stragglers<PS, SSG, FAST><<<side->blocks, kStragWarps * 32, tsm, side->stream>>>(a);
+    cudaEventRecord(side->join, side->stream);
+    if (walk_grid + side->blocks > (unsigned)slots) walk_grid = (unsigned)slots > (unsigned)side->blocks ? (unsigned)slots - side->blocks : 1u;
+  }
+  k_inverse_search<PS, WSG, FAST><<<walk_grid, kWarps * 32, smem, s>>>(a);
+  if (overlap && !side->reserve) {
+    // k_stragglers is launched behind the walk on the side stream: its blocks become resident as the walk's
+    // persistent blocks retire, so the hand-offs are worked on during the walk's tail instead of after it.
+    cudaStreamWaitEvent(side->stream, side->fork, 0);
+    k_stragglers<PS, SSG, FAST><<<side->blocks, kStragWarps * 32, tsm, side->stream>>>(a);
+    cudaEventRecord(side->join, side->stream);
+  }
+  if (a.stragglers) cudaMemsetAsync(a.straggler_count + 2, 1, sizeof(int), s);   // "walk finished": the entry count is final
   if (ev) cudaEventRecord(ev[2], s);
   if (a.stragglers) {
-    constexpr int SSG = (DIS_STRAG_SG8 && PS == 8) ? 8 : SG;   // shorter per-pass chains: the kernel is latency-bound
-    const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SSG>::G * kTile * kTileStride : 0;
-    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
-    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-    k_stragglers<PS, SSG, FAST><<<148 * DIS_STRAG_BLOCKS, kStragWarps * 32, tsm, s>>>(a);
+    if (overlap) cudaStreamWaitEvent(s, side->join, 0);
+    else k_stragglers<PS, SSG, FAST><<<148 * DIS_STRAG_BLOCKS, kStragWarps * 32, tsm, s>>>(a);
     ++n;
   }
   if (ev) cudaEventRecord(ev[3], s);
@@ -921,9 +984,9 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev) {
 
 }  // namespace
 
-int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev) {
+int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev, const SearchSide* side) {
   const bool fast = a.conv_eps2 > 0.f;
-#define DIS_CASE(PS, SG) case PS: return fast ? launch_ps<PS, SG, true>(a, s, ev) : launch_ps<PS, SG, false>(a, s, ev);
+#define DIS_CASE(PS, SG) case PS: return fast ? launch_ps<PS, SG, true>(a, s, ev, side) : launch_ps<PS, SG, false>(a, s, ev, side);
   switch (patch_size) {
     DIS_CASE(4, 4) DIS_CASE(6, 4) DIS_CASE(8, 4) DIS_CASE(10, 8) DIS_CASE(12, 8) DIS_CASE(16, 8)
     default: return -1;
