@@ -614,11 +614,14 @@ k_inverse_search(const SearchArgs A) {
       if (lane == 0) { atomicAdd(&A.counters[5], (unsigned long long)__popc(m)); atomicAdd(&A.counters[13], (unsigned long long)__popc(f)); } }
 #endif
 #pragma unroll
+    // a lane closer than kChunk passes to its budget steps through the slow path below (one pass per round),
+    // which keeps the budget test out of the loop
+    run = run && k + kChunk <= iters + 1;
     for (int it = 0; it < kChunk; ++it) {
       if (DIS_EARLY && it == DIS_EARLY && !__any_sync(kFull, run)) break;
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
       const uint4 e = cache[slot_of(bx, by) * 32];
-      run = run && e.x == bx && e.y == by && k <= iters;
+      run = run && e.x == bx && e.y == by;
       if (run) {
         ++k;
         const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
