@@ -67,7 +67,7 @@ struct dis_engine {
   std::vector<cudaStream_t> gstream;    // group streams (group 0 runs on `stream` itself)
   std::vector<cudaEvent_t> gdone;
   cudaEvent_t fork_ev = nullptr;
-  dis::SearchSide side = {nullptr, nullptr, nullptr, 0, 0};   // k_stragglers beside the walk (single-group runs)
+  dis::SearchSide side = {nullptr, nullptr, nullptr, 0};   // k_stragglers beside the walk (single-group runs)
   int n_groups = 1;                     // groups of the last run
   std::vector<cudaEvent_t> search_ev;   // [group][level][4]: before k_converge | before the walk | before k_stragglers | after
   int search_launches = 0;              // per group
@@ -286,6 +286,7 @@ int fetch_counters(dis_engine* e) {
           c[4], (double)c[5] / c[4], (double)c[13] / c[4], (double)c[6] / (c[5] ? c[5] : 1), (double)c[7] / c[4], (double)c[8] / (c[7] ? c[7] : 1),
           (double)c[12] / c[4], c[9], c[10], c[11], (double)c[10] / (c[11] ? c[11] : 1));
 #endif
+  if (c[15]) return fail(DIS_ERR_CUDA, "internal: k_stragglers timed out waiting for the walk's hand-offs; results are incomplete");
   e->stats.patch_iterations = c[0]; e->stats.sampled_iterations = c[1];
   e->stats.resets = c[2]; e->stats.start_oob = c[3];
   e->stats.kernel_launches = e->launches;
@@ -363,7 +364,6 @@ int dis_create(const dis_params* p, int device, dis_engine** out) {
   {
     const char* sb = getenv("DIS_SIDE_BLOCKS");          // 0 = run k_stragglers after the walk instead of beside it
     e->side.blocks = sb ? (unsigned)std::max(0, atoi(sb)) : 592u;
-    e->side.reserve = getenv("DIS_SIDE_RESERVE") ? 1 : 0;
     if (e->side.blocks > 0 &&
         (cudaStreamCreateWithFlags(&e->side.stream, cudaStreamNonBlocking) != cudaSuccess ||
          cudaEventCreateWithFlags(&e->side.fork, cudaEventDisableTiming) != cudaSuccess ||
@@ -445,8 +445,7 @@ int dis_download_flows(dis_engine* e, float* flow_out) {
   CU(cudaSetDevice(e->device));
   CU(cudaMemcpyAsync(flow_out, e->out.p, sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs,
                      cudaMemcpyDeviceToHost, e->stream));
-  CU(cudaStreamSynchronize(e->stream));
-  return DIS_OK;
+  return fetch_counters(e);   // synchronises; also surfaces the kernels' internal error flag
 }
 
 int dis_synchronize(dis_engine* e) {

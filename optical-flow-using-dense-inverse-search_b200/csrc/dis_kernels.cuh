@@ -33,7 +33,7 @@ struct SearchArgs {
   const float* init_override; // optional explicit per-patch init [pair][np][2] (PatchGrid API); else nullptr
   float* u_out;             // [pair][np][2]
   int* iters_out;           // [pair][np] or nullptr
-  unsigned long long* counters;  // [4]: patch_iterations, sampled_iterations, resets, start_oob (or nullptr)
+  unsigned long long* counters;  // [16]: patch_iterations, sampled_iterations, resets, start_oob, ...; [15] = internal error flag (or nullptr)
   void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
   int* straggler_count;     // [0] entries appended, [1] entries claimed by k_stragglers, [2] "walk finished" flag (device)
   int* work_counter;        // next patch index of the launch (device; zeroed by the launcher)
@@ -69,7 +69,7 @@ constexpr size_t kWalkBytesPerPatch = 32 + 16 * kWalkSeeds;   // walk_state + wa
 
 // host-callable launchers (each returns the number of kernels launched)
 // Optional second stream on which k_stragglers runs CONCURRENTLY with the walk (fork/join: timing-disabled events).
-struct SearchSide { cudaStream_t stream; cudaEvent_t fork, join; unsigned blocks; int reserve; };
+struct SearchSide { cudaStream_t stream; cudaEvent_t fork, join; unsigned blocks; };
 // ev: optional 4 events recorded before k_converge, before the walk, after the walk and after k_stragglers has joined
 int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev = nullptr,
                           const SearchSide* side = nullptr);

@@ -799,7 +799,10 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
         if (ld_volatile(ctl + 1) < cnt) { base = atomicAdd(ctl + 1, G::G); break; }
         if (done) break;                                     // nothing left and nothing more to come
         __nanosleep(400);
-        if (clock64() - t_start > 20000000000ll) break;      // safety net (~10 s): never spin forever
+        if (clock64() - t_start > 20000000000ll) {           // safety net (~10 s): never spin forever; the host reports it
+          if (A.counters) atomicExch(&A.counters[15], 1ull);
+          break;
+        }
       }
     }
     base = __shfl_sync(kFull, base, 0);
@@ -938,7 +941,6 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   constexpr int SSG = (DIS_STRAG_SG8 && PS == 8) ? 8 : SG;
   const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SSG>::G * kTile * kTileStride : 0;
   const bool overlap = a.stragglers && side && side->stream;   // k_stragglers runs beside the walk and eats its hand-offs as they come
-  unsigned walk_grid = blocks;
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) {
     const long long cap = total / 4 + 64 < a.straggler_cap ? total / 4 + 64 : a.straggler_cap;
@@ -958,23 +960,17 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   }
   if (ev) cudaEventRecord(ev[1], s);
   if (overlap) cudaEventRecord(side->fork, s);               // "convergence phase done"
-  if (overlap && side->reserve) {
-    // k_stragglers starts with the walk: its blocks (4 warps, ~150 registers) take one of the three block slots of
-    // `side->blocks` SMs, the walk gets the rest of the machine.
-    cudaStreamWaitEvent(side->stream, side->fork, 0);
-    k_stragglers<PS, SSG, FAST><<<side->blocks, kStragWarps * 32, tsm, side->stream>>>(a);
-    cudaEventRecord(side->join, side->stream);
-    if (walk_grid + side->blocks > (unsigned)slots) walk_grid = (unsigned)slots > (unsigned)side->blocks ? (unsigned)slots - side->blocks : 1u;
-  }
-  k_inverse_search<PS, WSG, FAST><<<walk_grid, kWarps * 32, smem, s>>>(a);
-  if (overlap && !side->reserve) {
+  k_inverse_search<PS, WSG, FAST><<<blocks, kWarps * 32, smem, s>>>(a);
+  if (a.stragglers) cudaMemsetAsync(a.straggler_count + 2, 1, sizeof(int), s);   // "walk finished": the entry count is final
+  if (overlap) {
     // k_stragglers is launched behind the walk on the side stream: its blocks become resident as the walk's
     // persistent blocks retire, so the hand-offs are worked on during the walk's tail instead of after it.
+    // (Enqueued after the flag's memset so that a host that serialises launches — CUDA_LAUNCH_BLOCKING, ncu —
+    // still terminates: the kernel then simply starts with the flag already set.)
     cudaStreamWaitEvent(side->stream, side->fork, 0);
     k_stragglers<PS, SSG, FAST><<<side->blocks, kStragWarps * 32, tsm, side->stream>>>(a);
     cudaEventRecord(side->join, side->stream);
   }
-  if (a.stragglers) cudaMemsetAsync(a.straggler_count + 2, 1, sizeof(int), s);   // "walk finished": the entry count is final
   if (ev) cudaEventRecord(ev[2], s);
   if (a.stragglers) {
     if (overlap) cudaStreamWaitEvent(s, side->join, 0);
