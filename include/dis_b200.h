@@ -192,6 +192,21 @@ DIS_API int dis_write_flo(const char* path, const float* flow, int w, int h);
 DIS_API int dis_read_flo(const char* path, float* flow, int w, int h);
 DIS_API int dis_read_flo_size(const char* path, int* w, int* h);
 
+/* ---- one large frame tiled by grid rows over several GPUs (BASELINE config 5) ------
+ * Replaces the same per-pair path as dis_run_pair_u8 (src/main.cpp:135-198) when the pair is split
+ * over N engines (one per GPU).  Every engine gets the whole pair; per level (coarsest first,
+ * level = scale - finest_scale) it searches the grid rows [row0, row1) (PatchGrid::inverse_search,
+ * src/patch_grid.cpp:99-106, restricted to those patches), the per-patch flows
+ * (Patch::get_u_vector, [num_patches][2] fp32, patch id = x*nph + y) are exchanged by the caller
+ * through DEVICE buffers on the engine's GPU (e.g. an NCCL all-gather), and the level is densified
+ * (src/patch_grid.cpp:121-182) redundantly on every engine.  Bit-identical to dis_run_pair_u8. */
+DIS_API int dis_tiled_begin(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, int h, int stride);
+DIS_API int dis_tiled_search(dis_engine* e, int level, int row0, int row1);
+DIS_API int dis_tiled_get_u(dis_engine* e, int level, void* device_dst);
+DIS_API int dis_tiled_set_u(dis_engine* e, int level, const void* device_src);
+DIS_API int dis_tiled_densify(dis_engine* e, int level);
+DIS_API int dis_tiled_finish(dis_engine* e, float* flow_out);
+
 /* Middlebury colour coding, draw_optical_flow(flow, dst, maxmotion) of src/color_coding.cpp:83-117
  * (called at src/main.cpp:200-201 with maxmotion = -1: the range is the field's own maximum).
  * flow: h x w x 2 fp32 host; bgr_out: h x w x 3 u8 host (B,G,R as cv::Mat CV_8UC3). */

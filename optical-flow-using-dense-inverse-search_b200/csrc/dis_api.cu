@@ -77,6 +77,7 @@ struct dis_engine {
   int w0 = 0, h0 = 0, W = 0, H = 0, left = 0, top = 0, pad = 0;
   int n_frames = 0, n_pairs = 0, stride_u8 = 0;
   bool have_run = false;
+  bool tiled = false;                   // between dis_tiled_begin and dis_tiled_finish
   bool stats_fetched = false;
   bool keep_iters = true;
   int max_groups = 1;                   // DIS_GROUPS overrides; measured: no gain on B200 (levels are work-bound, not tail-bound)
@@ -195,49 +196,64 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
 
 namespace {
 
-// The coarse-to-fine loop of src/optical_flow.cpp:67-90 for pairs [p0, p1) of the run on stream `st`.
-int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
+// Everything the search kernels need for level index s (= scale - finest) and pairs [p0, p1) of the run.
+dis::SearchArgs level_search_args(dis_engine* e, int g, int s, int p0, int p1) {
   const dis_params& p = e->prm;
   const int nl = (int)e->levels.size();
   char* sbase = e->stragglers.as<char>() + (size_t)g * e->straggler_stride;
+  Level& L = e->levels[s];
+  const dis_level_info& I = L.info;
+  dis::SearchArgs a;
+  memset(&a, 0, sizeof a);
+  a.planes = e->planes[I.scale];
+  a.pairs = e->pairs.as<int2>() + p0;
+  a.flow_prev = (s < nl - 1) ? e->levels[s + 1].flow.as<float>() + e->levels[s + 1].flow_stride * p0 : nullptr;
+  a.flow_prev_stride = (s < nl - 1) ? e->levels[s + 1].flow_stride : 0;
+  a.init_override = nullptr;
+  a.u_out = L.u.as<float>() + 2 * (size_t)I.num_patches * p0;
+  a.iters_out = e->keep_iters ? L.iters.as<int>() + (size_t)I.num_patches * p0 : nullptr;
+  a.counters = e->counters.as<unsigned long long>();
+  a.straggler_count = reinterpret_cast<int*>(sbase);
+  a.work_counter = reinterpret_cast<int*>(sbase) + 8;
+  a.stragglers = sbase + 64;
+  a.straggler_cap = e->straggler_cap;
+  a.walk_state = e->walk.as<char>() + 32 * (size_t)I.num_patches * p0;
+  a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * I.num_patches * p0;
+  a.n_pairs = p1 - p0;
+  a.share = getenv("DIS_SHARE") ? e->n_groups : 1;   // full-size grids: a later group fills the SMs an earlier group's tail leaves idle
+  a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
+  a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
+  a.warps_per_pair = (I.num_patches + 31) / 32;
+  a.iterations = p.max_iter; a.patnorm = p.patch_norm ? 1 : 0;
+  a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
+  a.out2max = sq_threshold(e->outlier); a.tile_margin = (int)ceilf(e->outlier) + 1;
+  a.conv_eps2 = p.conv_eps * p.conv_eps;
+  return a;
+}
+
+// PatchGrid::densification_and_create_dance_flow for level s, pairs [p0, p1)
+void level_densify(dis_engine* e, int s, int p0, int p1, cudaStream_t st) {
+  Level& L = e->levels[s];
+  const dis_level_info& I = L.info;
+  dis::DensifyArgs d;
+  d.u = L.u.as<float>() + 2 * (size_t)I.num_patches * p0;
+  d.dense = L.flow.as<float>() + L.flow_stride * p0; d.dense_stride = L.flow_stride;
+  d.n_pairs = p1 - p0; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
+  d.offw = I.offw; d.offh = I.offh; d.steps = I.steps; d.np = I.num_patches; d.ps = e->prm.patch_size;
+  e->launches += dis::launch_densify(d, st);
+}
+
+// The coarse-to-fine loop of src/optical_flow.cpp:67-90 for pairs [p0, p1) of the run on stream `st`.
+int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
+  const int nl = (int)e->levels.size();
   int launch = 0;
   for (int s = nl - 1; s >= 0; --s, ++launch) {
-    Level& L = e->levels[s];
-    const dis_level_info& I = L.info;
-    dis::SearchArgs a;
-    memset(&a, 0, sizeof a);
-    a.planes = e->planes[I.scale];
-    a.pairs = e->pairs.as<int2>() + p0;
-    a.flow_prev = (s < nl - 1) ? e->levels[s + 1].flow.as<float>() + e->levels[s + 1].flow_stride * p0 : nullptr;
-    a.flow_prev_stride = (s < nl - 1) ? e->levels[s + 1].flow_stride : 0;
-    a.init_override = nullptr;
-    a.u_out = L.u.as<float>() + 2 * (size_t)I.num_patches * p0;
-    a.iters_out = e->keep_iters ? L.iters.as<int>() + (size_t)I.num_patches * p0 : nullptr;
-    a.counters = e->counters.as<unsigned long long>();
-    a.straggler_count = reinterpret_cast<int*>(sbase);
-    a.work_counter = reinterpret_cast<int*>(sbase) + 8;
-    a.stragglers = sbase + 64;
-    a.straggler_cap = e->straggler_cap;
-    a.walk_state = e->walk.as<char>() + 32 * (size_t)I.num_patches * p0;
-    a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * I.num_patches * p0;
-    a.n_pairs = p1 - p0;
-    a.share = getenv("DIS_SHARE") ? e->n_groups : 1;   // full-size grids: a later group fills the SMs an earlier group's tail leaves idle
-    a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
-    a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
-    a.warps_per_pair = (I.num_patches + 31) / 32;
-    a.iterations = p.max_iter; a.patnorm = p.patch_norm ? 1 : 0;
-    a.lb = L.lb; a.ub_w = L.ub_w; a.ub_h = L.ub_h;
-    a.out2max = sq_threshold(e->outlier); a.tile_margin = (int)ceilf(e->outlier) + 1;
-    a.conv_eps2 = p.conv_eps * p.conv_eps;
+    const dis::SearchArgs a = level_search_args(e, g, s, p0, p1);
     cudaEvent_t* ev = &e->search_ev[4 * (g * nl + launch)];
-    const int n = dis::launch_inverse_search(a, p.patch_size, st, ev, (e->n_groups == 1 && e->side.stream) ? &e->side : nullptr);
+    const int n = dis::launch_inverse_search(a, e->prm.patch_size, st, ev, (e->n_groups == 1 && e->side.stream) ? &e->side : nullptr);
     if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
     e->launches += n;
-    dis::DensifyArgs d;
-    d.u = a.u_out; d.dense = L.flow.as<float>() + L.flow_stride * p0; d.dense_stride = L.flow_stride;
-    d.n_pairs = p1 - p0; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
-    d.offw = I.offw; d.offh = I.offh; d.steps = I.steps; d.np = I.num_patches; d.ps = p.patch_size;
-    e->launches += dis::launch_densify(d, st);
+    level_densify(e, s, p0, p1, st);
   }
   return DIS_OK;
 }
@@ -949,6 +965,93 @@ int dis_grid_get_patch(dis_grid* g, int i, float* ref_xy, float* u_xy) {
     else { u_xy[0] = 0.f; u_xy[1] = 0.f; }   // Patch::reset_patch, src/patch.cpp:102-116
   }
   return DIS_OK;
+}
+
+// ---- one large frame tiled by grid rows over several GPUs (BASELINE.json config 5) ---------
+// Within a level the patches are independent and densification is a local gather, so every GPU searches the
+// patches of its band of grid rows, the per-patch flows u are exchanged (a few MB per level; the caller does it,
+// e.g. an NCCL all-gather over NVLink), and every GPU densifies the whole level redundantly (< 1 % of the work).
+// The result is bit-identical to the single-GPU run.
+int dis_tiled_begin(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, int h, int stride) {
+  if (!e || !a || !b) return fail(DIS_ERR_PARAM, "null argument");
+  if (w <= 0 || h <= 0 || stride < w) return fail(DIS_ERR_PARAM, "bad frame geometry");
+  CU(cudaSetDevice(e->device));
+  const int padw = div_pad(w, e->prm.coarsest_scale), padh = div_pad(h, e->prm.coarsest_scale);
+  e->w0 = w; e->h0 = h; e->left = padw / 2; e->top = padh / 2;
+  if (int rc = setup_run(e, w + padw, h + padh, e->prm.patch_size, 2, 1)) return rc;
+  const size_t fbytes = (size_t)w * h;
+  if (e->frames_u8.ensure(fbytes * 2)) return fail(DIS_ERR_ALLOC, "cudaMalloc(frames) failed");
+  CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>(), w, a, stride, w, h, cudaMemcpyHostToDevice, e->stream));
+  CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>() + fbytes, w, b, stride, w, h, cudaMemcpyHostToDevice, e->stream));
+  const int2 pr = make_int2(0, 1);
+  CU(cudaMemcpyAsync(e->pairs.p, &pr, sizeof pr, cudaMemcpyHostToDevice, e->stream));
+  e->stride_u8 = w;
+  e->launches = 0;
+  if (int rc = run_pyramid_u8(e, w)) return rc;
+  CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
+  for (Level& L : e->levels)   // patches outside this GPU's bands are filled in by dis_tiled_set_u
+    CU(cudaMemsetAsync(L.u.p, 0, 2 * sizeof(float) * (size_t)L.info.num_patches, e->stream));
+  const int nl = (int)e->levels.size();
+  while ((int)e->search_ev.size() < 4 * nl) { cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev); }
+  e->n_groups = 1; e->search_launches = nl;
+  CU(cudaStreamSynchronize(e->stream));   // `pr` is on the stack
+  e->have_run = false; e->tiled = true;
+  return DIS_OK;
+}
+
+int dis_tiled_search(dis_engine* e, int level, int row0, int row1) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  const int nl = (int)e->levels.size();
+  if (level < 0 || level >= nl) return fail(DIS_ERR_PARAM, "level out of range");
+  const dis_level_info& I = e->levels[level].info;
+  if (row0 < 0 || row1 > I.nph || row0 > row1) return fail(DIS_ERR_PARAM, "grid rows out of range");
+  if (row0 == row1) return DIS_OK;   // an empty band (more GPUs than grid rows)
+  CU(cudaSetDevice(e->device));
+  dis::SearchArgs a = level_search_args(e, 0, level, 0, 1);
+  a.band_y0 = row0; a.band_h = row1 - row0;
+  cudaEvent_t* ev = &e->search_ev[4 * (nl - 1 - level)];
+  const int n = dis::launch_inverse_search(a, e->prm.patch_size, e->stream, ev, e->side.stream ? &e->side : nullptr);
+  if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
+  e->launches += n;
+  CU(cudaGetLastError());
+  return DIS_OK;
+}
+
+static int tiled_copy_u(dis_engine* e, int level, void* dst, const void* src, bool get) {
+  if (!e || (get ? !dst : !src)) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  if (level < 0 || level >= (int)e->levels.size()) return fail(DIS_ERR_PARAM, "level out of range");
+  CU(cudaSetDevice(e->device));
+  Level& L = e->levels[level];
+  const size_t bytes = 2 * sizeof(float) * (size_t)L.info.num_patches;
+  CU(cudaMemcpyAsync(get ? dst : L.u.p, get ? L.u.p : src, bytes, cudaMemcpyDeviceToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));   // the caller's buffers live on other streams (torch / NCCL)
+  return DIS_OK;
+}
+int dis_tiled_get_u(dis_engine* e, int level, void* device_dst) { return tiled_copy_u(e, level, device_dst, nullptr, true); }
+int dis_tiled_set_u(dis_engine* e, int level, const void* device_src) { return tiled_copy_u(e, level, nullptr, device_src, false); }
+
+int dis_tiled_densify(dis_engine* e, int level) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  if (level < 0 || level >= (int)e->levels.size()) return fail(DIS_ERR_PARAM, "level out of range");
+  CU(cudaSetDevice(e->device));
+  level_densify(e, level, 0, 1, e->stream);
+  CU(cudaGetLastError());
+  return DIS_OK;
+}
+
+int dis_tiled_finish(dis_engine* e, float* flow_out) {
+  if (!e || !flow_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  CU(cudaSetDevice(e->device));
+  if (int rc = run_epilogue(e)) return rc;
+  CU(cudaMemcpyAsync(flow_out, e->out.p, sizeof(float) * 2 * (size_t)e->w0 * e->h0, cudaMemcpyDeviceToHost, e->stream));
+  e->stats.patches = 0;
+  for (const Level& L : e->levels) e->stats.patches += (unsigned long long)L.info.num_patches;
+  e->have_run = true; e->stats_fetched = false; e->tiled = false;
+  return fetch_counters(e);
 }
 
 // ---- colour coding (src/color_coding.cpp:83-117) -------------------------------------------------

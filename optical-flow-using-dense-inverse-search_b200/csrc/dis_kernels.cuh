@@ -43,6 +43,7 @@ struct SearchArgs {
   int n_pairs;
   int width, height, pad, tmp_w;
   int npw, nph, offw, offh, steps, np;
+  int band_y0, band_h;      // grid rows covered by this launch (band_h <= 0: all of them)
   int warps_per_pair;
   int share;                // this launch may use 1/share of the GPU's resident block slots (concurrent groups)
   int iterations, patnorm;

@@ -376,13 +376,18 @@ struct WarpSmem {
   int list[32];                      // lanes to serve, in rank order
 };
 
-// Geometry of patch `idx` of the launch (idx = pair * np + id; id = x*nph + y, src/patch_grid.cpp:39-49).
-struct PatchGeom { int pair, pid, rx, ry; };
-__device__ __forceinline__ PatchGeom patch_geom(const SearchArgs& A, int idx) {
+// Geometry of work item `w` of the launch.  A launch covers the grid rows [band_y0, band_y0 + band_h) of every
+// pair (the whole grid unless a large frame is row-tiled over several GPUs): w = (pair * npw + x) * band_h + y'.
+// pid = x*nph + y is the reference's patch id (src/patch_grid.cpp:39-49); sidx = pair * np + pid indexes u / iters.
+struct PatchGeom { int pair, pid, rx, ry, sidx; };
+__device__ __forceinline__ PatchGeom patch_geom(const SearchArgs& A, int w) {
   PatchGeom g;
-  g.pair = idx / A.np;
-  g.pid = idx - g.pair * A.np;
-  const int gx = g.pid / A.nph, gy = g.pid - gx * A.nph;
+  const int npb = A.npw * A.band_h;
+  g.pair = w / npb;
+  const int r = w - g.pair * npb;
+  const int gx = r / A.band_h, gy = A.band_y0 + (r - gx * A.band_h);
+  g.pid = gx * A.nph + gy;
+  g.sidx = g.pair * A.np + g.pid;
   g.rx = gx * A.steps + A.offw;
   g.ry = gy * A.steps + A.offh;
   return g;
@@ -412,15 +417,18 @@ __device__ __forceinline__ float2 patch_init(const SearchArgs& A, int idx, int p
 #ifndef DIS_CONV_BLOCKS
 #define DIS_CONV_BLOCKS 2
 #endif
-constexpr int kConvWarps = DIS_CONV_WARPS;
+// ps <= 8: 8 warps x 2 blocks at <= 128 registers; larger patches keep more elements per lane and get the full register file
+__host__ __device__ constexpr int conv_warps(int ps) { return ps <= 8 ? DIS_CONV_WARPS : 4; }
+__host__ __device__ constexpr int conv_blocks(int ps) { return ps <= 8 ? DIS_CONV_BLOCKS : 1; }
 template <int PS, int SG, bool FAST>
-__global__ void __launch_bounds__(kConvWarps * 32, DIS_CONV_BLOCKS) k_converge(const SearchArgs A) {
+__global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_converge(const SearchArgs A) {
   using G = Geom<PS, SG>;
+  constexpr int kConvWarps = conv_warps(PS);
   const int lane = threadIdx.x & 31, sub = lane / SG, sl = lane % SG;
   const int gwarp = blockIdx.x * kConvWarps + (threadIdx.x >> 5);
   const int nwarps = gridDim.x * kConvWarps;
   const int tw = A.tmp_w;
-  const int total = A.n_pairs * A.np;
+  const int total = A.n_pairs * A.npw * A.band_h;
   const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
   const int iters = A.iterations;
   int eoff[G::NPL];
@@ -438,7 +446,7 @@ __global__ void __launch_bounds__(kConvWarps * 32, DIS_CONV_BLOCKS) k_converge(c
     const int idx = have ? base + sub : total - 1;
     const PatchGeom g = patch_geom(A, idx);
     const float refx = (float)g.rx, refy = (float)g.ry;
-    const float2 in = patch_init(A, idx, g.pair, refx, refy);
+    const float2 in = patch_init(A, g.sidx, g.pair, refx, refy);
     float ux = in.x, uy = in.y;                               // Patch::inverse_search_start, src/patch.cpp:119-154
     float px = refx + ux, py = refy + uy;
     const float stx = px, sty = py;
@@ -505,8 +513,8 @@ __global__ void __launch_bounds__(kConvWarps * 32, DIS_CONV_BLOCKS) k_converge(c
       reinterpret_cast<float4*>(states)[2 * (size_t)idx + 1] = make_float4(ws.p, ws.q, ws.l, ws.u11);
       c_sampled += ns;
       if (!active) {                                          // finished here: Patch::get_u_vector
-        reinterpret_cast<float2*>(A.u_out)[idx] = make_float2(ux, uy);
-        if (A.iters_out) A.iters_out[idx] = k;
+        reinterpret_cast<float2*>(A.u_out)[g.sidx] = make_float2(ux, uy);
+        if (A.iters_out) A.iters_out[g.sidx] = k;
         c_iters += (unsigned long long)k;
         c_resets += was_reset ? 1u : 0u;
         c_oob += oob ? 1u : 0u;
@@ -540,7 +548,7 @@ k_inverse_search(const SearchArgs A) {
   WarpSmem& W = reinterpret_cast<WarpSmem*>(smem_raw)[threadIdx.x >> 5];
   uint4* cache = &W.cache[0][lane];                           // slot s at cache[s * 32]
   const int tw = A.tmp_w;
-  const int total = A.n_pairs * A.np;
+  const int total = A.n_pairs * A.npw * A.band_h;
   const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
   const int sub = lane / SG, sl = lane % SG;
   int eoff[G::NPL];
@@ -585,7 +593,7 @@ k_inverse_search(const SearchArgs A) {
             pair = g.pair;
             coff = (g.ry + A.pad) * tw + (g.rx + A.pad);
             refx = (float)g.rx; refy = (float)g.ry;
-            const float2 in = patch_init(A, idx, g.pair, refx, refy);
+            const float2 in = patch_init(A, g.sidx, g.pair, refx, refy);
             inx = in.x; iny = in.y;
             stx = refx + inx; sty = refy + iny;                // Patch::inverse_search_start, src/patch.cpp:119-154
             ux = w0.x; uy = w0.y;
@@ -613,10 +621,10 @@ k_inverse_search(const SearchArgs A) {
     { const unsigned m = __ballot_sync(kFull, run), f = __ballot_sync(kFull, state == ST_FREE);
       if (lane == 0) { atomicAdd(&A.counters[5], (unsigned long long)__popc(m)); atomicAdd(&A.counters[13], (unsigned long long)__popc(f)); } }
 #endif
-#pragma unroll
     // a lane closer than kChunk passes to its budget steps through the slow path below (one pass per round),
     // which keeps the budget test out of the loop
     run = run && k + kChunk <= iters + 1;
+#pragma unroll
     for (int it = 0; it < kChunk; ++it) {
       if (DIS_EARLY && it == DIS_EARLY && !__any_sync(kFull, run)) break;
       const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
@@ -671,7 +679,7 @@ k_inverse_search(const SearchArgs A) {
             const int slot = atomicAdd(A.straggler_count, 1);
             if (slot < A.straggler_cap) {
               Straggler* rec = reinterpret_cast<Straggler*>(A.stragglers) + slot;
-              *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(pair), __int_as_float(idx - pair * A.np), ux, uy);
+              *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(pair), __int_as_float(patch_geom(A, idx).pid), ux, uy);
               __threadfence();
               *reinterpret_cast<volatile int*>(&rec->k) = k;     // publish
               state = ST_FREE;     // results and counters come from k_stragglers
@@ -737,8 +745,9 @@ k_inverse_search(const SearchArgs A) {
       }
     } else if (needs) ++waited;
     if (fin) {                                               // Patch::get_u_vector of a finished patch
-      reinterpret_cast<float2*>(A.u_out)[idx] = make_float2(ux, uy);
-      if (A.iters_out) A.iters_out[idx] = k;
+      const int sidx = patch_geom(A, idx).sidx;
+      reinterpret_cast<float2*>(A.u_out)[sidx] = make_float2(ux, uy);
+      if (A.iters_out) A.iters_out[sidx] = k;
       c_iters += (unsigned long long)k;
       c_resets += was_reset ? 1u : 0u;
       state = ST_FREE;
@@ -926,7 +935,8 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   // persistent warps: lanes fetch patches from a global counter until the level is done
-  const long long total = (long long)a.n_pairs * a.np;
+  if (a.band_h <= 0) { a.band_y0 = 0; a.band_h = a.nph; }
+  const long long total = (long long)a.n_pairs * a.npw * a.band_h;
   const long long want = (total + kWarps * 32 - 1) / (kWarps * 32);
   const long long slots = (148 * walk_blocks(PS, WSG) + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
   const unsigned blocks = (unsigned)(want < slots ? want : slots);
@@ -952,8 +962,9 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   }
   if (ev) cudaEventRecord(ev[0], s);
   {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
+    constexpr int kConvWarps = conv_warps(PS);
     const long long cwant = (total + kConvWarps * Geom<PS, SG>::G - 1) / (kConvWarps * Geom<PS, SG>::G);
-    const long long cslots = 148LL * (DIS_CONV_BLOCKS > 1 ? DIS_CONV_BLOCKS * 4 : 12) / (a.share > 1 ? a.share : 1);
+    const long long cslots = 148LL * (conv_blocks(PS) > 1 ? conv_blocks(PS) * 4 : 12) / (a.share > 1 ? a.share : 1);
     // one shared-memory carve-out for all three kernels: kernels with different carve-outs cannot share an SM
     cudaFuncSetAttribute(k_converge<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     k_converge<PS, SG, FAST><<<(unsigned)(cwant < cslots ? cwant : cslots), kConvWarps * 32, 0, s>>>(a);

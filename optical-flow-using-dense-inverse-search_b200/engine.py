@@ -51,7 +51,8 @@ ABI_SYMBOLS = [
     "dis_get_plane", "dis_get_stats", "dis_grid_create", "dis_grid_create_single", "dis_grid_destroy", "dis_grid_init", "dis_grid_set_target",
     "dis_grid_init_from_prev_flow", "dis_grid_set_patch_init", "dis_grid_inverse_search", "dis_grid_densify",
     "dis_grid_num_patches", "dis_grid_get_patch", "dis_write_flo", "dis_read_flo", "dis_read_flo_size",
-    "dis_color_code", "dis_color_code_pair",
+    "dis_color_code", "dis_color_code_pair", "dis_tiled_begin", "dis_tiled_search", "dis_tiled_get_u", "dis_tiled_set_u",
+    "dis_tiled_densify", "dis_tiled_finish",
 ]
 
 
@@ -100,6 +101,7 @@ class Engine:
         self._h = C.c_void_p()
         _chk(self.lib.dis_create(C.byref(self.params), int(device), C.byref(self._h)))
         self._shape = None
+        self.device = int(device)
 
     def close(self):
         if self._h:
@@ -120,6 +122,31 @@ class Engine:
         out = np.empty((h, w, 2), np.float32)
         _chk(self.lib.dis_run_pair_u8(self._h, a.ctypes.data_as(_u8p), b.ctypes.data_as(_u8p), w, h, w,
                                       out.ctypes.data_as(_fp)))
+        return out
+
+    # ---- one large frame tiled by grid rows over several engines ------------
+    def tiled_begin(self, a: np.ndarray, b: np.ndarray) -> None:
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        h, w = a.shape
+        _chk(self.lib.dis_tiled_begin(self._h, a.ctypes.data_as(_u8p), b.ctypes.data_as(_u8p), w, h, w))
+        self._shape = (1, h, w)
+
+    def tiled_search(self, level: int, row0: int, row1: int) -> None:
+        _chk(self.lib.dis_tiled_search(self._h, int(level), int(row0), int(row1)))
+
+    def tiled_get_u(self, level: int, device_ptr: int) -> None:
+        _chk(self.lib.dis_tiled_get_u(self._h, int(level), C.c_void_p(device_ptr)))
+
+    def tiled_set_u(self, level: int, device_ptr: int) -> None:
+        _chk(self.lib.dis_tiled_set_u(self._h, int(level), C.c_void_p(device_ptr)))
+
+    def tiled_densify(self, level: int) -> None:
+        _chk(self.lib.dis_tiled_densify(self._h, int(level)))
+
+    def tiled_finish(self) -> np.ndarray:
+        _, h, w = self._shape
+        out = np.empty((h, w, 2), np.float32)
+        _chk(self.lib.dis_tiled_finish(self._h, out.ctypes.data_as(_fp)))
         return out
 
     def color_code(self, flow: np.ndarray, maxmotion: float = -1.0) -> np.ndarray:

@@ -50,3 +50,75 @@ def gather_results(local: List, dist=None) -> List:
     out = [None] * dist.get_world_size()
     dist.all_gather_object(out, local)
     return out
+
+
+# ---- one large frame tiled by grid rows over several GPUs (BASELINE.json config 5) --------
+def band_rows(nph: int, world: int, rank: int) -> Tuple[int, int]:
+    """Grid rows [row0, row1) of a level searched by `rank`: contiguous bands, heights differing by at most 1."""
+    return shard_pairs(nph, world, rank)
+
+
+def _merge_bands(parts, npw: int, nph: int, world: int):
+    """parts[r]: the full-size u tensor [npw*nph, 2] of rank r (valid in its own band) -> merged tensor."""
+    import torch
+    out = torch.empty_like(parts[0])
+    v = out.view(npw, nph, 2)
+    for r in range(world):
+        r0, r1 = band_rows(nph, world, r)
+        v[:, r0:r1] = parts[r].view(npw, nph, 2)[:, r0:r1]
+    return out
+
+
+def run_pair_tiled(engine, a, b, rank: int, world: int, dist=None):
+    """One frame pair split over `world` GPUs (one engine / process each): per level every rank searches the
+    patches of its band of grid rows, the per-patch flows are all-gathered over NCCL (a few MB per level, no
+    pixel data), and every rank densifies the whole level.  Returns the full flow on every rank, bit-identical
+    to engine.run_pair(a, b).  `dist` = torch.distributed (initialised, NCCL) or None when world == 1."""
+    import torch
+    dev = torch.device("cuda", engine.device)
+    engine.tiled_begin(a, b)
+    for level in range(engine.num_levels() - 1, -1, -1):
+        li = engine.level_info(level)
+        r0, r1 = band_rows(li["nph"], world, rank)
+        engine.tiled_search(level, r0, r1)
+        if world > 1:
+            mine = torch.empty((li["num_patches"], 2), dtype=torch.float32, device=dev)
+            engine.tiled_get_u(level, mine.data_ptr())
+            bh = -(-li["nph"] // world)                       # bands padded to one height for the all-gather
+            send = torch.zeros((li["npw"], bh, 2), dtype=torch.float32, device=dev)
+            send[:, : r1 - r0] = mine.view(li["npw"], li["nph"], 2)[:, r0:r1]
+            recv = torch.empty((world, li["npw"], bh, 2), dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(recv, send)
+            full = mine.view(li["npw"], li["nph"], 2)
+            for r in range(world):
+                q0, q1 = band_rows(li["nph"], world, r)
+                full[:, q0:q1] = recv[r, :, : q1 - q0]
+            torch.cuda.synchronize(dev)
+            engine.tiled_set_u(level, mine.data_ptr())
+        engine.tiled_densify(level)
+    return engine.tiled_finish()
+
+
+def run_pair_tiled_emulated(engines, a, b):
+    """The same schedule with all `len(engines)` ranks living in ONE process (engines may share a GPU): the
+    exchange is a device-side merge instead of an NCCL all-gather.  Used by the single-GPU parity test."""
+    import torch
+    world = len(engines)
+    for e in engines:
+        e.tiled_begin(a, b)
+    for level in range(engines[0].num_levels() - 1, -1, -1):
+        li = engines[0].level_info(level)
+        parts = []
+        for r, e in enumerate(engines):
+            r0, r1 = band_rows(li["nph"], world, r)
+            e.tiled_search(level, r0, r1)
+            t = torch.empty((li["num_patches"], 2), dtype=torch.float32, device=torch.device("cuda", e.device))
+            e.tiled_get_u(level, t.data_ptr())
+            parts.append(t)
+        for r, e in enumerate(engines):
+            dev = torch.device("cuda", e.device)
+            merged = _merge_bands([p.to(dev) for p in parts], li["npw"], li["nph"], world)
+            torch.cuda.synchronize(dev)
+            e.tiled_set_u(level, merged.data_ptr())
+            e.tiled_densify(level)
+    return [e.tiled_finish() for e in engines]

@@ -64,3 +64,11 @@ def test_gloo_world2_reduction_and_gather():
         assert red["device_ms"] == 11.0                       # MAX over ranks
         assert [x for part in got for x in part] == list(range(49))
     assert dis_b200.parallel.reduce_stats({k: 1 for k in dis_b200.parallel.STAT_KEYS}, 2.5)["device_ms"] == 2.5
+
+
+def test_band_rows_partition_the_grid():
+    from dis_b200.parallel import band_rows
+    for nph, world in [(1080, 8), (28, 8), (3, 8), (220, 2)]:
+        bands = [band_rows(nph, world, r) for r in range(world)]
+        assert bands[0][0] == 0 and bands[-1][1] == nph
+        assert all(bands[i][1] == bands[i + 1][0] for i in range(world - 1))
