@@ -67,6 +67,8 @@ struct dis_engine {
   std::vector<cudaStream_t> gstream;    // group streams (group 0 runs on `stream` itself)
   std::vector<cudaEvent_t> gdone;
   cudaEvent_t fork_ev = nullptr;
+  cudaStream_t copy_stream = nullptr;   // host-buffer calls: flows of a slice of pairs go home while the next slice is searched
+  std::vector<cudaEvent_t> slice_ev;
   dis::SearchSide side = {nullptr, nullptr, nullptr, 0};   // k_stragglers beside the walk (single-group runs)
   int n_groups = 1;                     // groups of the last run
   std::vector<cudaEvent_t> search_ev;   // [group][level][4]: before k_converge | before the walk | before k_stragglers | after
@@ -79,6 +81,7 @@ struct dis_engine {
   bool have_run = false;
   bool tiled = false;                   // between dis_tiled_begin and dis_tiled_finish
   bool stats_fetched = false;
+  bool out_sent = false;                // the last run already copied its flows to the caller's buffer
   bool keep_iters = true;
   int max_groups = 1;                   // DIS_GROUPS overrides; measured: no gain on B200 (levels are work-bound, not tail-bound)
 
@@ -243,22 +246,51 @@ void level_densify(dis_engine* e, int s, int p0, int p1, cudaStream_t st) {
   e->launches += dis::launch_densify(d, st);
 }
 
+int run_epilogue(dis_engine* e, int p0, int p1);
+
 // The coarse-to-fine loop of src/optical_flow.cpp:67-90 for pairs [p0, p1) of the run on stream `st`.
-int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st) {
+// host_out != null (host-buffer calls, one group): the finest level runs in slices of pairs, and each slice's
+// cropped flows are copied to the caller's buffer on `copy_stream` while the next slice is being searched; the
+// epilogue and the download are then done when this returns (the engine's stream waits for the last copy).
+int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st, float* host_out = nullptr) {
   const int nl = (int)e->levels.size();
   int launch = 0;
+  const dis::SearchSide* side = (e->n_groups == 1 && e->side.stream) ? &e->side : nullptr;
   for (int s = nl - 1; s >= 0; --s, ++launch) {
-    const dis::SearchArgs a = level_search_args(e, g, s, p0, p1);
     cudaEvent_t* ev = &e->search_ev[4 * (g * nl + launch)];
-    const int n = dis::launch_inverse_search(a, e->prm.patch_size, st, ev, (e->n_groups == 1 && e->side.stream) ? &e->side : nullptr);
-    if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
-    e->launches += n;
-    level_densify(e, s, p0, p1, st);
+    int slices = 1;
+    if (s == 0 && host_out) {
+      static const char* env = getenv("DIS_OUT_SLICES");
+      slices = env ? atoi(env) : (p1 - p0 >= 32 ? 4 : p1 - p0 >= 8 ? 2 : 1);
+      slices = std::max(1, std::min(slices, p1 - p0));
+      while ((int)e->slice_ev.size() < slices + 1) {
+        cudaEvent_t x; CU(cudaEventCreateWithFlags(&x, cudaEventDisableTiming)); e->slice_ev.push_back(x);
+      }
+    }
+    for (int c = 0; c < slices; ++c) {
+      const int q0 = p0 + (int)((long long)(p1 - p0) * c / slices), q1 = p0 + (int)((long long)(p1 - p0) * (c + 1) / slices);
+      const dis::SearchArgs a = level_search_args(e, g, s, q0, q1);
+      const int n = dis::launch_inverse_search(a, e->prm.patch_size, st, c == 0 ? ev : nullptr, side);   // timings: first slice only
+      if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
+      e->launches += n;
+      level_densify(e, s, q0, q1, st);
+      if (s == 0 && host_out) {
+        if (int rc = run_epilogue(e, q0, q1)) return rc;
+        const size_t off = 2 * (size_t)e->w0 * e->h0 * q0, cnt = 2 * (size_t)e->w0 * e->h0 * (q1 - q0);
+        CU(cudaEventRecord(e->slice_ev[c], st));
+        CU(cudaStreamWaitEvent(e->copy_stream, e->slice_ev[c], 0));
+        CU(cudaMemcpyAsync(host_out + off, e->out.as<float>() + off, sizeof(float) * cnt, cudaMemcpyDeviceToHost, e->copy_stream));
+      }
+    }
+    if (s == 0 && host_out) {
+      CU(cudaEventRecord(e->slice_ev[slices], e->copy_stream));
+      CU(cudaStreamWaitEvent(st, e->slice_ev[slices], 0));
+    }
   }
   return DIS_OK;
 }
 
-int run_levels(dis_engine* e) {
+int run_levels(dis_engine* e, float* host_out = nullptr) {
   const int nl = (int)e->levels.size();
   CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
   const int G = std::max(1, std::min(std::min(kMaxGroups, e->max_groups), e->n_pairs));
@@ -274,12 +306,16 @@ int run_levels(dis_engine* e) {
   if (!e->fork_ev) CU(cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming));
   e->n_groups = G;
   e->search_launches = nl;
+  if (host_out && (G > 1 || e->n_pairs < 8 || (getenv("DIS_OUT_SLICES") && atoi(getenv("DIS_OUT_SLICES")) <= 1))) host_out = nullptr;
+  if (host_out && !e->copy_stream) CU(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+  if (host_out && e->out.ensure(sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
+  e->out_sent = host_out != nullptr;
   if (G > 1) CU(cudaEventRecord(e->fork_ev, e->stream));
   for (int g = G - 1; g >= 0; --g) {          // group 0 last: it runs on the engine's own stream
     const int p0 = (int)((long long)e->n_pairs * g / G), p1 = (int)((long long)e->n_pairs * (g + 1) / G);
     cudaStream_t st = g == 0 ? e->stream : e->gstream[g - 1];
     if (g > 0) CU(cudaStreamWaitEvent(st, e->fork_ev, 0));
-    if (int rc = run_levels_group(e, g, p0, p1, st)) return rc;
+    if (int rc = run_levels_group(e, g, p0, p1, st, host_out)) return rc;
     if (g > 0) CU(cudaEventRecord(e->gdone[g - 1], st));
   }
   for (int g = 1; g < G; ++g) CU(cudaStreamWaitEvent(e->stream, e->gdone[g - 1], 0));
@@ -324,20 +360,23 @@ int run_pyramid_u8(dis_engine* e, int stride) {
   return DIS_OK;
 }
 
-// finest dense flow -> cropped output (src/main.cpp:192-198), device to device
-int run_epilogue(dis_engine* e) {
+// finest dense flow -> cropped output (src/main.cpp:192-198), device to device, pairs [p0, p1)
+int run_epilogue(dis_engine* e, int p0, int p1) {
   Level& L = e->levels[0];
   if (e->out.ensure(sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
+  const float* dense = L.flow.as<float>() + L.flow_stride * p0;
+  float* out = e->out.as<float>() + 2 * (size_t)e->w0 * e->h0 * p0;
   if (e->prm.finest_scale == 0)
-    e->launches += dis::launch_crop(L.flow.as<float>(), L.flow_stride, L.info.width, L.info.height, e->left, e->top,
-                                    e->out.as<float>(), e->w0, e->h0, e->n_pairs, e->stream);
+    e->launches += dis::launch_crop(dense, L.flow_stride, L.info.width, L.info.height, e->left, e->top,
+                                    out, e->w0, e->h0, p1 - p0, e->stream);
   else
-    e->launches += dis::launch_upsample_crop(L.flow.as<float>(), L.flow_stride, L.info.width, L.info.height,
-                                             e->prm.finest_scale, e->left, e->top, e->out.as<float>(), e->w0, e->h0,
-                                             e->n_pairs, e->stream);
+    e->launches += dis::launch_upsample_crop(dense, L.flow_stride, L.info.width, L.info.height,
+                                             e->prm.finest_scale, e->left, e->top, out, e->w0, e->h0,
+                                             p1 - p0, e->stream);
   CU(cudaGetLastError());
   return DIS_OK;
 }
+int run_epilogue(dis_engine* e) { return run_epilogue(e, 0, e->n_pairs); }
 
 int div_pad(int dim, int coarsest) {   // src/main.cpp:139-149
   const int sf = 1 << coarsest, r = dim % sf;
@@ -411,6 +450,8 @@ void dis_destroy(dis_engine* e) {
   for (cudaEvent_t ev : e->gdone) cudaEventDestroy(ev);
   for (cudaStream_t st : e->gstream) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
   if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+  for (cudaEvent_t ev : e->slice_ev) cudaEventDestroy(ev);
+  if (e->copy_stream) { cudaStreamSynchronize(e->copy_stream); cudaStreamDestroy(e->copy_stream); }
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -549,18 +590,24 @@ int run_frames(dis_engine* e, const uint8_t* const* fptr, int n_frames, int w, i
   if (int rc = setup_run(e, w + padw, h + padh, e->prm.patch_size, n_frames, n_pairs)) return rc;
   const size_t fbytes = (size_t)w * h;   // frames are stored densely on the device
   if (e->frames_u8.ensure(fbytes * n_frames)) return fail(DIS_ERR_ALLOC, "cudaMalloc(frames) failed");
-  for (int f = 0; f < n_frames; ++f)
-    CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>() + fbytes * f, w, fptr[f], stride, w, h,
-                         cudaMemcpyHostToDevice, e->stream));
+  bool dense = stride == w;                                   // one copy when the frames are back to back in host memory
+  for (int f = 1; f < n_frames && dense; ++f) dense = fptr[f] == fptr[f - 1] + fbytes;
+  if (dense) CU(cudaMemcpyAsync(e->frames_u8.p, fptr[0], fbytes * n_frames, cudaMemcpyHostToDevice, e->stream));
+  else
+    for (int f = 0; f < n_frames; ++f)
+      CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>() + fbytes * f, w, fptr[f], stride, w, h,
+                           cudaMemcpyHostToDevice, e->stream));
   std::vector<int2> pr(n_pairs);
   for (int i = 0; i < n_pairs; ++i) pr[i] = make_int2(first[i], second[i]);
   CU(cudaMemcpyAsync(e->pairs.p, pr.data(), sizeof(int2) * n_pairs, cudaMemcpyHostToDevice, e->stream));
   e->stride_u8 = w;
   e->launches = 0;
   if (int rc = run_pyramid_u8(e, w)) return rc;
-  if (int rc = run_levels(e)) return rc;
-  if (int rc = run_epilogue(e)) return rc;
-  CU(cudaMemcpyAsync(flow_out, e->out.p, sizeof(float) * 2 * fbytes * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  if (int rc = run_levels(e, flow_out)) return rc;
+  if (!e->out_sent) {           // else: cropped and copied slice by slice inside the finest level
+    if (int rc = run_epilogue(e)) return rc;
+    CU(cudaMemcpyAsync(flow_out, e->out.p, sizeof(float) * 2 * fbytes * n_pairs, cudaMemcpyDeviceToHost, e->stream));
+  }
   return fetch_counters(e);   // synchronises; pr stays alive until here
 }
 

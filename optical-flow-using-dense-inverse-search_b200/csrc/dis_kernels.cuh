@@ -51,6 +51,7 @@ struct SearchArgs {
   float out2max;            // largest fp32 s with sqrtf(s) <= outlierthresh: |start-pos| > thr <=> s > out2max
   float conv_eps2;          // conv_eps^2; 0 = off (reference behaviour)
   int handoff_misses;       // walk -> k_stragglers after this many misses of a patch (set by the launcher from the launch size)
+  float early_step;         // k_converge -> k_stragglers when the last passes still move by this much (px); 0 = never (set by the launcher)
   int tile_margin;          // ceil(outlierthresh) + 1: how far (px) a tap base can move from the start position's before a reset
 };
 

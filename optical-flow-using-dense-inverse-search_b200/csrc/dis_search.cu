@@ -470,6 +470,7 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
     Wn.bx = -1; Wn.by = -1;
     int k = 0;
     unsigned ns = 0, fifo = 0;
+    float moved = 0.f;                                        // largest |delta u| component of the last three passes
     __syncwarp();
 #pragma unroll
     for (int i = lane; i < G::G * kSlots; i += 32) img_warp[i] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
@@ -493,26 +494,40 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
         const float2 d = lu.solve(sg.x, sg.y);                // src/patch.cpp:176
         if (sl == 0 && pass >= kN1 - kSeed)
           cache_insert<1, true>(img, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y)));
+        if (pass >= kN1 - 3) moved = fmaxf(moved, fmaxf(fabsf(d.x), fabsf(d.y)));
         ++k; ++ns;
         ux = ux - d.x; uy = uy - d.y;                         // src/patch.cpp:179
         px = refx + ux; py = refy + uy;                       // src/patch.cpp:182
         if (FAST) { if (d.x * d.x + d.y * d.y < A.conv_eps2) active = false; }
       }
     }
+    // A patch that still moves by a sizeable step after kN1 passes almost never settles (its walk would miss on
+    // most passes): it goes to k_stragglers right away instead of after handoff_misses expensive walk misses.
+    bool handed = false;
+    if (have && active && sl == 0 && A.stragglers && A.early_step > 0.f && moved >= A.early_step) {
+      const int slot = atomicAdd(A.straggler_count, 1);
+      if (slot < A.straggler_cap) {
+        Straggler* rec = reinterpret_cast<Straggler*>(A.stragglers) + slot;
+        *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(g.pair), __int_as_float(g.pid), ux, uy);
+        __threadfence();
+        *reinterpret_cast<volatile int*>(&rec->k) = k;        // publish
+        handed = true;
+      } else atomicSub(A.straggler_count, 1);
+    }
     __syncwarp();
-    if (__any_sync(kFull, active)) {                          // cache images of the batch's patches, coalesced
+    if (__any_sync(kFull, active && !handed)) {                          // cache images of the batch's patches, coalesced
 #pragma unroll
       for (int i = lane; i < G::G * kSlots; i += 32)
         if (base + i / kSlots < total) seeds[(size_t)base * kSlots + i] = img_warp[i];
     }
     if (have && sl == 0) {
       WalkState ws;
-      ws.ux = ux; ws.uy = uy; ws.k = active ? k : -1; ws.swap = (lu.swap ? 1 : 0) | (int)(fifo << 8);
+      ws.ux = ux; ws.uy = uy; ws.k = active && !handed ? k : -1; ws.swap = (lu.swap ? 1 : 0) | (int)(fifo << 8);
       ws.p = lu.p; ws.q = lu.q; ws.l = lu.l; ws.u11 = lu.u11;
       reinterpret_cast<float4*>(states)[2 * (size_t)idx] = make_float4(ws.ux, ws.uy, __int_as_float(ws.k), __int_as_float(ws.swap));
       reinterpret_cast<float4*>(states)[2 * (size_t)idx + 1] = make_float4(ws.p, ws.q, ws.l, ws.u11);
       c_sampled += ns;
-      if (!active) {                                          // finished here: Patch::get_u_vector
+      if (!active) {                                          // finished here: Patch::get_u_vector (handed: k_stragglers reports)
         reinterpret_cast<float2*>(A.u_out)[g.sidx] = make_float2(ux, uy);
         if (A.iters_out) A.iters_out[g.sidx] = k;
         c_iters += (unsigned long long)k;
@@ -776,6 +791,7 @@ k_inverse_search(const SearchArgs A) {
 // Everything a straggler can touch lies within outlierthresh of its start position (beyond it the patch is
 // reset, src/patch.cpp:185), so ps 8 stages that neighbourhood of the second image — kTile x kTile taps
 // around the start — in shared memory once per patch: the ~950-pass chain then never waits on L2.
+constexpr float kEarlyStep = 0.3f;   // px; measured on the bench workload: 0.1 ... 1 equivalent (+1 %), below 0.03 the stragglers take over
 constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
 constexpr int kStragWarps = 4;
 template <int PS, int SG, bool FAST>
@@ -947,6 +963,8 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
     int t0 = 24, t1 = 48, t2 = 128, t3 = 384;
     if (env) sscanf(env, "%d,%d,%d,%d", &t0, &t1, &t2, &t3);
     a.handoff_misses = total < 200000 ? t0 : total < 600000 ? t1 : total < 2000000 ? t2 : t3;
+    static const char* env_e = getenv("DIS_EARLY_STEP");
+    a.early_step = env_e ? (float)atof(env_e) : kEarlyStep;
   }
   constexpr int SSG = (DIS_STRAG_SG8 && PS == 8) ? 8 : SG;
   const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SSG>::G * kTile * kTileStride : 0;
