@@ -51,6 +51,9 @@ struct SearchArgs {
   float out2max;            // largest fp32 s with sqrtf(s) <= outlierthresh: |start-pos| > thr <=> s > out2max
   float conv_eps2;          // conv_eps^2; 0 = off (reference behaviour)
   int handoff_misses;       // walk -> k_stragglers after this many misses of a patch (set by the launcher from the launch size)
+  int walk_chunks;          // the walk's fast phase runs up to this many chunks of kChunk passes per round ...
+  int walk_minrun;          // ... while at least this many lanes of the warp are still running
+  int walk_age;             // rounds a waiting patch may be held back for a fuller service round
   float early_step;         // k_converge -> k_stragglers when the last passes still move by this much (px); 0 = never (set by the launcher)
   int tile_margin;          // ceil(outlierthresh) + 1: how far (px) a tap base can move from the start position's before a reset
 };

@@ -51,7 +51,7 @@ __device__ __forceinline__ int slot_of(unsigned bx, unsigned by) { return ((bx &
 // XOR distance, in slot index space, between way 0 and way w of a set (way bit 0 = bit 1 of y, bits 1.. = bits 1.. of x)
 __host__ __device__ constexpr int way_xor(int w) { return ((w & 1) << 1) | ((w >> 1) << 3); }
 #ifndef DIS_CHUNK
-#define DIS_CHUNK 8
+#define DIS_CHUNK 6
 #endif
 #ifndef DIS_AGE
 #define DIS_AGE 4
@@ -636,70 +636,82 @@ k_inverse_search(const SearchArgs A) {
     { const unsigned m = __ballot_sync(kFull, run), f = __ballot_sync(kFull, state == ST_FREE);
       if (lane == 0) { atomicAdd(&A.counters[5], (unsigned long long)__popc(m)); atomicAdd(&A.counters[13], (unsigned long long)__popc(f)); } }
 #endif
-    // a lane closer than kChunk passes to its budget steps through the slow path below (one pass per round),
-    // which keeps the budget test out of the loop
-    run = run && k + kChunk <= iters + 1;
+    // A round is up to walk_chunks times {kChunk passes probing only the predicted way; lanes that left the chunk
+    // probe all four ways of the set and, on a hit, step one pass and rejoin}; it ends early once fewer than
+    // walk_minrun lanes are running.  Lanes with a first-seen position then wait for the service below.
+    // (A lane closer than kChunk passes to its budget steps through the four-way probe, one pass per chunk,
+    // which keeps the budget test out of the inner loop.)
+    bool missed = false;
+    int chunk = 0;
+#pragma unroll 1
+    do {
+      run = run && k + kChunk <= iters + 1;
 #pragma unroll
-    for (int it = 0; it < kChunk; ++it) {
-      if (DIS_EARLY && it == DIS_EARLY && !__any_sync(kFull, run)) break;
-      const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-      const uint4 e = cache[slot_of(bx, by) * 32];
-      run = run && e.x == bx && e.y == by;
-      if (run) {
-        ++k;
-        const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
-        ux = ux - dx; uy = uy - dy;                         // src/patch.cpp:179
-        px = refx + ux; py = refy + uy;                     // src/patch.cpp:182
-        if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) { run = false; fin = true; } }
+      for (int it = 0; it < kChunk; ++it) {
+        if (DIS_EARLY && it == DIS_EARLY && !__any_sync(kFull, run)) break;
+        const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
+        const uint4 e = cache[slot_of(bx, by) * 32];
+        run = run && e.x == bx && e.y == by;
+        if (run) {
+          ++k;
+          const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
+          ux = ux - dx; uy = uy - dy;                         // src/patch.cpp:179
+          px = refx + ux; py = refy + uy;                     // src/patch.cpp:182
+          if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) { run = false; fin = true; } }
+        }
       }
-    }
+      const bool probe = state == ST_RUN && !run && !fin && !missed;
+      if (__any_sync(kFull, probe)) {
+        if (probe) {
+          const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
+          const int p = slot_of(bx, by);
+          uint4 e = cache[p * 32];
+          bool hit = e.x == bx && e.y == by;
+#pragma unroll
+          for (int w = 1; w < kWays; ++w) {
+            const uint4 o = cache[(p ^ way_xor(w)) * 32];
+            if (o.x == bx && o.y == by) { e = o; hit = true; }
+          }
+          if (hit) {
+#ifdef DIS_DEBUG_STATS
+            atomicAdd(&A.counters[9], 1ull);
+#endif
+            if (k > iters) fin = true;                        // src/patch.cpp:199-201 (position already vetted)
+            else {
+              ++k;
+              const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
+              ux = ux - dx; uy = uy - dy;
+              px = refx + ux; py = refy + uy;
+              run = true;
+              if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) { run = false; fin = true; } }
+            }
+          } else missed = true;
+        }
+      }
+    } while (++chunk < A.walk_chunks && __popc(__ballot_sync(kFull, run)) >= A.walk_minrun);
 #ifdef DIS_DEBUG_STATS
     { int adv = k - dbg_k0;
       for (int o = 16; o > 0; o >>= 1) adv += __shfl_xor_sync(kFull, adv, o);
       if (lane == 0) atomicAdd(&A.counters[6], (unsigned long long)adv); }
 #endif
-    // ---- lanes that left the fast phase: probe all four ways of the set ---------------------------
-    if (state == ST_RUN && !run && !fin) {
-      const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);
-      const int p = slot_of(bx, by);
-      uint4 e = cache[p * 32];
-      bool hit = e.x == bx && e.y == by;
-#pragma unroll
-      for (int w = 1; w < kWays; ++w) {
-        const uint4 o = cache[(p ^ way_xor(w)) * 32];
-        if (o.x == bx && o.y == by) { e = o; hit = true; }
-      }
-      if (hit) {
-#ifdef DIS_DEBUG_STATS
-        atomicAdd(&A.counters[9], 1ull);
-#endif
-        if (k > iters) fin = true;                          // src/patch.cpp:199-201 (position already vetted)
+    if (missed) {
+      // a first-seen position: it owes its reset test and a sample
+      streak = (k == k_posted + 1) ? streak + 1 : 1;
+      k_posted = k;
+      state = ST_WAIT;
+      if (((streak >= kStreakLimit && k >= kHandoffMinIter) || misses >= A.handoff_misses) && A.stragglers) {
+        // the orbit does not settle: hand the patch to k_stragglers
+        if (must_reset(px, py, stx, sty, A)) { ux = inx; uy = iny; was_reset = true; fin = true; }
+        else if (k > iters) fin = true;
         else {
-          ++k;
-          const float dx = __uint_as_float(e.z), dy = __uint_as_float(e.w);
-          ux = ux - dx; uy = uy - dy;
-          px = refx + ux; py = refy + uy;
-          if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) fin = true; }
-        }
-      } else {
-        // a first-seen position: it owes its reset test and a sample
-        streak = (k == k_posted + 1) ? streak + 1 : 1;
-        k_posted = k;
-        state = ST_WAIT;
-        if (((streak >= kStreakLimit && k >= kHandoffMinIter) || misses >= A.handoff_misses) && A.stragglers) {
-          // the orbit does not settle: hand the patch to k_stragglers
-          if (must_reset(px, py, stx, sty, A)) { ux = inx; uy = iny; was_reset = true; fin = true; }
-          else if (k > iters) fin = true;
-          else {
-            const int slot = atomicAdd(A.straggler_count, 1);
-            if (slot < A.straggler_cap) {
-              Straggler* rec = reinterpret_cast<Straggler*>(A.stragglers) + slot;
-              *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(pair), __int_as_float(patch_geom(A, idx).pid), ux, uy);
-              __threadfence();
-              *reinterpret_cast<volatile int*>(&rec->k) = k;     // publish
-              state = ST_FREE;     // results and counters come from k_stragglers
-            } else { atomicSub(A.straggler_count, 1); streak = 0; }
-          }
+          const int slot = atomicAdd(A.straggler_count, 1);
+          if (slot < A.straggler_cap) {
+            Straggler* rec = reinterpret_cast<Straggler*>(A.stragglers) + slot;
+            *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(pair), __int_as_float(patch_geom(A, idx).pid), ux, uy);
+            __threadfence();
+            *reinterpret_cast<volatile int*>(&rec->k) = k;     // publish
+            state = ST_FREE;     // results and counters come from k_stragglers
+          } else { atomicSub(A.straggler_count, 1); streak = 0; }
         }
       }
     }
@@ -714,7 +726,7 @@ k_inverse_search(const SearchArgs A) {
       const int nwait = __popc(wait_mask);
       const int rem = nwait % G::G;
       const bool others = __ballot_sync(kFull, state == ST_RUN && !fin) != 0;
-      const bool aged = __any_sync(kFull, needs && (waited >= DIS_AGE || misses >= DIS_HEAVY));   // frequent missers are not made to wait
+      const bool aged = __any_sync(kFull, needs && (waited >= A.walk_age || misses >= DIS_HEAVY));   // frequent missers are not made to wait
       const int nserv = (!others || 2 * rem >= G::G || aged) ? nwait : nwait - rem;
       const int rank = __popc(wait_mask & ((1u << lane) - 1u));
       served = needs && rank < nserv;
@@ -791,6 +803,7 @@ k_inverse_search(const SearchArgs A) {
 // Everything a straggler can touch lies within outlierthresh of its start position (beyond it the patch is
 // reset, src/patch.cpp:185), so ps 8 stages that neighbourhood of the second image — kTile x kTile taps
 // around the start — in shared memory once per patch: the ~950-pass chain then never waits on L2.
+constexpr long long kStragWideBelow = 0;   // patches per launch
 constexpr float kEarlyStep = 0.3f;   // px; measured on the bench workload: 0.1 ... 1 equivalent (+1 %), below 0.03 the stragglers take over
 constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
 constexpr int kStragWarps = 4;
@@ -816,12 +829,14 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
     // ---- claim the next batch of G entries.  The kernel may run concurrently with the walk (ctl[2] == 0):
     //      entries are then consumed as they are published; a claimed slot that is still empty is waited for
     //      until the walk has finished, after which ctl[0] is final. ------------------------------------------
-    int base = -1;
+    int base = -1, nclaim = 0;
     if (lane == 0) {
       for (;;) {
         const int done = ld_volatile(ctl + 2);
         const int cnt = min(ld_volatile(ctl), A.straggler_cap);
-        if (ld_volatile(ctl + 1) < cnt) { base = atomicAdd(ctl + 1, G::G); break; }
+        const int claimed = ld_volatile(ctl + 1);
+        // no more than what has been appended: a warp does not sit on empty slots while hand-offs trickle in
+        if (claimed < cnt) { nclaim = min(G::G, cnt - claimed); base = atomicAdd(ctl + 1, nclaim); break; }
         if (done) break;                                     // nothing left and nothing more to come
         __nanosleep(400);
         if (clock64() - t_start > 20000000000ll) {           // safety net (~10 s): never spin forever; the host reports it
@@ -831,9 +846,10 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
       }
     }
     base = __shfl_sync(kFull, base, 0);
+    nclaim = __shfl_sync(kFull, nclaim, 0);
     if (base < 0) break;
     bool have = false;
-    if (sl == 0) {
+    if (sl == 0 && sub < nclaim) {
       for (;;) {
         if (ld_volatile(&list[base + sub < A.straggler_cap ? base + sub : 0].k) >= 0 && base + sub < A.straggler_cap) { have = true; break; }
         if (ld_volatile(ctl + 2) && base + sub >= min(ld_volatile(ctl), A.straggler_cap)) break;   // walk finished: the slot stays empty
@@ -963,11 +979,35 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
     int t0 = 24, t1 = 48, t2 = 128, t3 = 384;
     if (env) sscanf(env, "%d,%d,%d,%d", &t0, &t1, &t2, &t3);
     a.handoff_misses = total < 200000 ? t0 : total < 600000 ? t1 : total < 2000000 ? t2 : t3;
+    {   // per size class: chunks per round, lanes that must still run to go on, service ageing
+      static const char* env_t = getenv("DIS_WALK_TUNE");
+      int t[12] = {10, 24, DIS_AGE, 10, 24, DIS_AGE, 10, 24, DIS_AGE, 10, 24, DIS_AGE};   // measured: tools/sweep2.sh, DESIGN.md 3.2
+      if (env_t) sscanf(env_t, "%d,%d,%d:%d,%d,%d:%d,%d,%d:%d,%d,%d", t, t + 1, t + 2, t + 3, t + 4, t + 5, t + 6, t + 7, t + 8, t + 9, t + 10, t + 11);
+      const int c = total < 200000 ? 0 : total < 600000 ? 1 : total < 2000000 ? 2 : 3;
+      a.walk_chunks = t[3 * c]; a.walk_minrun = t[3 * c + 1]; a.walk_age = t[3 * c + 2];
+    }
     static const char* env_e = getenv("DIS_EARLY_STEP");
     a.early_step = env_e ? (float)atof(env_e) : kEarlyStep;
   }
-  constexpr int SSG = (DIS_STRAG_SG8 && PS == 8) ? 8 : SG;
-  const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SSG>::G * kTile * kTileStride : 0;
+  // k_stragglers: 4 lanes per patch (ps 8) have the fewest instructions per sample; 8 lanes per patch have the
+  // shorter dependent chain per pass, which is what bounds a small launch (its last hand-offs run alone).
+  static const char* env_w = getenv("DIS_STRAG_WIDE");
+  const long long wide_below = env_w ? atoll(env_w) : kStragWideBelow;
+  const bool wide = PS == 8 && SG == 4 && (DIS_STRAG_SG8 || total < wide_below);
+  auto strag = [&](unsigned nblocks, cudaStream_t st) {
+    if (wide) {
+      constexpr int WS = PS == 8 ? 8 : SG;
+      const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, WS>::G * kTile * kTileStride : 0;
+      cudaFuncSetAttribute(k_stragglers<PS, WS, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
+      cudaFuncSetAttribute(k_stragglers<PS, WS, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      k_stragglers<PS, WS, FAST><<<nblocks, kStragWarps * 32, tsm, st>>>(a);
+    } else {
+      const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SG>::G * kTile * kTileStride : 0;
+      cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
+      cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+      k_stragglers<PS, SG, FAST><<<nblocks, kStragWarps * 32, tsm, st>>>(a);
+    }
+  };
   const bool overlap = a.stragglers && side && side->stream;   // k_stragglers runs beside the walk and eats its hand-offs as they come
   cudaMemsetAsync(a.work_counter, 0, sizeof(int), s);
   if (a.stragglers) {
@@ -975,8 +1015,6 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
     a.straggler_cap = (int)cap;
     cudaMemsetAsync(a.straggler_count, 0, 4 * sizeof(int), s);
     cudaMemsetAsync(a.stragglers, 0xff, (size_t)cap * kStragglerBytes, s);
-    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
-    cudaFuncSetAttribute(k_stragglers<PS, SSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
   }
   if (ev) cudaEventRecord(ev[0], s);
   {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
@@ -997,13 +1035,13 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
     // (Enqueued after the flag's memset so that a host that serialises launches — CUDA_LAUNCH_BLOCKING, ncu —
     // still terminates: the kernel then simply starts with the flag already set.)
     cudaStreamWaitEvent(side->stream, side->fork, 0);
-    k_stragglers<PS, SSG, FAST><<<side->blocks, kStragWarps * 32, tsm, side->stream>>>(a);
+    strag(side->blocks, side->stream);
     cudaEventRecord(side->join, side->stream);
   }
   if (ev) cudaEventRecord(ev[2], s);
   if (a.stragglers) {
     if (overlap) cudaStreamWaitEvent(s, side->join, 0);
-    else k_stragglers<PS, SSG, FAST><<<148 * DIS_STRAG_BLOCKS, kStragWarps * 32, tsm, s>>>(a);
+    else strag(148 * DIS_STRAG_BLOCKS, s);
     ++n;
   }
   if (ev) cudaEventRecord(ev[3], s);
