@@ -46,18 +46,18 @@ constexpr int kSlots = kWalkSeeds;    // cache entries per patch: 4 sets (bit 0 
 static_assert(kSlots == 16 || kSlots == 32, "cache geometry");
 constexpr int kWays = kSlots / 4;
 constexpr int kWayBits = kSlots == 32 ? 3 : 2;
-// Slot predicted for a position.  16 slots: (4x + y) mod 16 — one LEA + one LOP3, and on the position traces of the
-// bench workload 37 % fewer hits in a non-predicted way than "low 2 bits of x above low 2 bits of y" (the orbit of a
+// Slot predicted for a position.  16 slots: (5x + y) mod 16 — the best of the lattice hashes (ax + by) mod 16 on the
+// position traces of the bench workload: half as many hits in a non-predicted way as "low 2 bits of x above low 2 bits of y" (the orbit of a
 // patch spreads over more ulps in y, whose coordinates are smaller, than in x).  32 slots: low 3 bits of x above low 2 of y.
 __device__ __forceinline__ int slot_of(unsigned bx, unsigned by) {
-  return kSlots == 16 ? (int)((4u * bx + by) & 15u) : (int)(((bx & (kSlots / 4 - 1)) << 2) | (by & 3));
+  return kSlots == 16 ? (int)((5u * bx + by) & 15u) : (int)(((bx & (kSlots / 4 - 1)) << 2) | (by & 3));
 }
 // &cache[slot_of(bx, by) * 32] for the walk's layout (slot s of a lane at cache[s * 32]) in three instructions:
 // the slot number is formed in the top four bits, where the wrap-around of the shifts is the "mod 16".
 __device__ __forceinline__ const uint4* slot_ptr32(const uint4* cache, unsigned bx, unsigned by) {
   static_assert(kSlots == 16 || kSlots == 32, "");
   if (kSlots != 16) return cache + slot_of(bx, by) * 32;
-  const unsigned top = (bx << 30) + (by << 28);
+  const unsigned top = bx * 0x50000000u + (by << 28);
   return reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(cache) + (top >> 19));
 }
 // XOR distance, in slot index space, between way 0 and way w of a set (way bit 0 = bit 1 of y, bits 1.. = bits 1.. of x)
