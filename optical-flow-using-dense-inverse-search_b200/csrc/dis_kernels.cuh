@@ -54,6 +54,8 @@ struct SearchArgs {
   int walk_chunks;          // the walk's fast phase runs up to this many chunks of kChunk passes per round ...
   int walk_minrun;          // ... while at least this many lanes of the warp are still running
   int walk_age;             // rounds a waiting patch may be held back for a fuller service round
+  int conv_slack;           // ... all but this many of its patches
+  int conv_min;             // k_converge: a warp's batch may leave after this many passes once each of its patches has re-sampled a seen position
   float early_step;         // k_converge -> k_stragglers when the last passes still move by this much (px); 0 = never (set by the launcher)
   int tile_margin;          // ceil(outlierthresh) + 1: how far (px) a tap base can move from the start position's before a reset
 };

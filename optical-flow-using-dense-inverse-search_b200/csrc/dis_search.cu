@@ -337,19 +337,20 @@ __device__ __forceinline__ bool must_reset(float px, float py, float stx, float 
 // Insert {position bits -> delta_u} into a patch's 16-slot cache image (slot s at cache[s * STRIDE]).
 // The entry goes to the way predicted by bit 1 of x and y; an entry already there moves to the set's
 // FIFO victim way.  DEDUP: skip the insertion when the position is already present in its set.
+// Returns true when (DEDUP) the position was already there.
 template <int STRIDE, bool DEDUP>
-__device__ __forceinline__ void cache_insert(uint4* cache, unsigned& fifo, const uint4 e) {
+__device__ __forceinline__ bool cache_insert(uint4* cache, unsigned& fifo, const uint4 e) {
   const int p = slot_of(e.x, e.y);
   const uint4 old = cache[p * STRIDE];
   if (DEDUP) {
-    if (old.x == e.x && old.y == e.y) return;
+    if (old.x == e.x && old.y == e.y) return true;
     bool found = false;
 #pragma unroll
     for (int w = 1; w < kWays; ++w) {
       const uint4 o = cache[(p ^ way_xor(w)) * STRIDE];
       found = found || (o.x == e.x && o.y == e.y);
     }
-    if (found) return;
+    if (found) return true;
   }
   if (old.x != 0xffffffffu) {
     const int set = ((p >> 1) & 2) | (p & 1);
@@ -359,6 +360,7 @@ __device__ __forceinline__ void cache_insert(uint4* cache, unsigned& fifo, const
     if (q != p) cache[q * STRIDE] = old;                      // the displaced entry moves there
   }
   cache[p * STRIDE] = e;
+  return false;
 }
 
 enum : int { ST_RUN = 0, ST_WAIT = 1, ST_FREE = 3 };
@@ -494,6 +496,8 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
         else if (k > iters) active = false;                                                              // src/patch.cpp:199-201
       }
       if (pass == kN1 || !__any_sync(kFull, active)) break;
+      // (nearly) every patch of the batch has come back to a position it sampled before: the rest is cheaper in the walk
+      if (pass >= A.conv_min && __popc(__ballot_sync(kFull, sl == 0 && active && (fifo >> 31) == 0u)) <= A.conv_slack) break;
       float2 sg;
       if constexpr (PS == 8) {
         const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
@@ -505,7 +509,8 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
       if (active) {
         const float2 d = lu.solve(sg.x, sg.y);                // src/patch.cpp:176
         if (sl == 0 && pass >= kN1 - kSeed)
-          cache_insert<1, true>(img, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y)));
+          if (cache_insert<1, true>(img, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y))))
+            fifo |= 0x80000000u;                                // "settled" rides in the unused top bit
         if (pass >= kN1 - 3) moved = fmaxf(moved, fmaxf(fabsf(d.x), fabsf(d.y)));
         ++k; ++ns;
         ux = ux - d.x; uy = uy - d.y;                         // src/patch.cpp:179
@@ -534,7 +539,7 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
     }
     if (have && sl == 0) {
       WalkState ws;
-      ws.ux = ux; ws.uy = uy; ws.k = active && !handed ? k : -1; ws.swap = (lu.swap ? 1 : 0) | (int)(fifo << 8);
+      ws.ux = ux; ws.uy = uy; ws.k = active && !handed ? k : -1; ws.swap = (lu.swap ? 1 : 0) | (int)((fifo & 0xffffu) << 8);
       ws.p = lu.p; ws.q = lu.q; ws.l = lu.l; ws.u11 = lu.u11;
       reinterpret_cast<float4*>(states)[2 * (size_t)idx] = make_float4(ws.ux, ws.uy, __int_as_float(ws.k), __int_as_float(ws.swap));
       reinterpret_cast<float4*>(states)[2 * (size_t)idx + 1] = make_float4(ws.p, ws.q, ws.l, ws.u11);
@@ -816,6 +821,7 @@ k_inverse_search(const SearchArgs A) {
 // reset, src/patch.cpp:185), so ps 8 stages that neighbourhood of the second image — kTile x kTile taps
 // around the start — in shared memory once per patch: the ~950-pass chain then never waits on L2.
 constexpr long long kStragWideBelow = 0;   // patches per launch
+constexpr int kConvMin = 12;      // passes; >= kN1 = never
 constexpr float kEarlyStep = 0.3f;   // px; measured on the bench workload: 0.1 ... 1 equivalent (+1 %), below 0.03 the stragglers take over
 constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
 constexpr int kStragWarps = 4;
@@ -998,6 +1004,10 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
       const int c = total < 200000 ? 0 : total < 600000 ? 1 : total < 2000000 ? 2 : 3;
       a.walk_chunks = t[3 * c]; a.walk_minrun = t[3 * c + 1]; a.walk_age = t[3 * c + 2];
     }
+    static const char* env_c = getenv("DIS_CONV_MIN");
+    a.conv_min = env_c ? atoi(env_c) : kConvMin;
+    static const char* env_s = getenv("DIS_CONV_SLACK");
+    a.conv_slack = env_s ? atoi(env_s) : 2;
     static const char* env_e = getenv("DIS_EARLY_STEP");
     a.early_step = env_e ? (float)atof(env_e) : kEarlyStep;
   }
