@@ -259,16 +259,34 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st, floa
   for (int s = nl - 1; s >= 0; --s, ++launch) {
     cudaEvent_t* ev = &e->search_ev[4 * (g * nl + launch)];
     int slices = 1;
+    std::vector<int> cut{p0, p1};         // slice c = pairs [cut[c], cut[c + 1])
     if (s == 0 && host_out) {
+      // DIS_OUT_SLICES: a count (equal slices) or a comma list of weights, e.g. "4,3,2,1": the last slice's
+      // copy is the only one nothing hides, so a tapering split shortens the exposed tail.
       static const char* env = getenv("DIS_OUT_SLICES");
-      slices = env ? atoi(env) : (p1 - p0 >= 32 ? 4 : p1 - p0 >= 8 ? 2 : 1);
-      slices = std::max(1, std::min(slices, p1 - p0));
+      std::vector<double> wt;
+      if (env && strchr(env, ',')) {
+        for (const char* q = env; q && *q; q = strchr(q, ',') ? strchr(q, ',') + 1 : nullptr) wt.push_back(std::max(0.0, atof(q)));
+      } else {
+        const int n = env ? atoi(env) : (p1 - p0 >= 32 ? 4 : p1 - p0 >= 8 ? 2 : 1);
+        wt.assign(std::max(1, std::min(n, p1 - p0)), 1.0);
+      }
+      double tot = 0, run = 0;
+      for (double x : wt) tot += x;
+      cut.assign(1, p0);
+      for (double x : wt) {
+        run += x;
+        const int q = tot > 0 ? p0 + (int)std::llround((p1 - p0) * run / tot) : p1;
+        if (q > cut.back()) cut.push_back(std::min(q, p1));
+      }
+      if (cut.back() != p1) cut.push_back(p1);
+      slices = (int)cut.size() - 1;
       while ((int)e->slice_ev.size() < slices + 1) {
         cudaEvent_t x; CU(cudaEventCreateWithFlags(&x, cudaEventDisableTiming)); e->slice_ev.push_back(x);
       }
     }
     for (int c = 0; c < slices; ++c) {
-      const int q0 = p0 + (int)((long long)(p1 - p0) * c / slices), q1 = p0 + (int)((long long)(p1 - p0) * (c + 1) / slices);
+      const int q0 = cut[c], q1 = cut[c + 1];
       const dis::SearchArgs a = level_search_args(e, g, s, q0, q1);
       const int n = dis::launch_inverse_search(a, e->prm.patch_size, st, c == 0 ? ev : nullptr, side);   // timings: first slice only
       if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
