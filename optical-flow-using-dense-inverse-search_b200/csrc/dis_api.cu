@@ -267,8 +267,10 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st, floa
       std::vector<double> wt;
       if (env && strchr(env, ',')) {
         for (const char* q = env; q && *q; q = strchr(q, ',') ? strchr(q, ',') + 1 : nullptr) wt.push_back(std::max(0.0, atof(q)));
+      } else if (!env && p1 - p0 >= 32) {
+        wt = {3.0, 1.0};   // measured on the 49-pair sequence (profiles/r1k_e2e_slices.log): every further slice costs a launch tail
       } else {
-        const int n = env ? atoi(env) : (p1 - p0 >= 32 ? 4 : p1 - p0 >= 8 ? 2 : 1);
+        const int n = env ? atoi(env) : (p1 - p0 >= 8 ? 2 : 1);
         wt.assign(std::max(1, std::min(n, p1 - p0)), 1.0);
       }
       double tot = 0, run = 0;

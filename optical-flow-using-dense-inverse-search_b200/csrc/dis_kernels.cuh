@@ -35,7 +35,8 @@ struct SearchArgs {
   int* iters_out;           // [pair][np] or nullptr
   unsigned long long* counters;  // [16]: patch_iterations, sampled_iterations, resets, start_oob, ...; [15] = internal error flag (or nullptr)
   void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
-  int* straggler_count;     // [0] entries appended, [1] entries claimed by k_stragglers, [2] "walk finished" flag (device)
+  int* straggler_count;     // [0] entries appended, [1] entries claimed by k_stragglers, [2] "walk finished" flag,
+                            // [3] blocks of the walk that have started (device)
   int* work_counter;        // next patch index of the launch (device; zeroed by the launcher)
   void* walk_state;         // [n_pairs*np] 32-byte hand-off records of the convergence phase
   void* walk_seeds;         // [n_pairs*np][kWalkSeeds] uint4 {pos bits x, y, delta_u x, y}
@@ -54,6 +55,7 @@ struct SearchArgs {
   int walk_chunks;          // the walk's fast phase runs up to this many chunks of kChunk passes per round ...
   int walk_minrun;          // ... while at least this many lanes of the warp are still running
   int walk_age;             // rounds a waiting patch may be held back for a fuller service round
+  int walk_grid;            // blocks of the walk's launch (k_stragglers yields its slot while fewer have started)
   int conv_slack;           // ... all but this many of its patches
   int conv_min;             // k_converge: a warp's batch may leave after this many passes once each of its patches has re-sampled a seen position
   float early_step;         // k_converge -> k_stragglers when the last passes still move by this much (px); 0 = never (set by the launcher)

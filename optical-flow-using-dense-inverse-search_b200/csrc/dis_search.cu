@@ -579,6 +579,7 @@ k_inverse_search(const SearchArgs A) {
   const int lane = threadIdx.x & 31;
   WarpSmem& W = reinterpret_cast<WarpSmem*>(smem_raw)[threadIdx.x >> 5];
   uint4* cache = &W.cache[0][lane];                           // slot s at cache[s * 32]
+  if (threadIdx.x == 0 && A.stragglers) atomicAdd(A.straggler_count + 3, 1);   // "this block of the walk is resident"
   const int tw = A.tmp_w;
   const int total = A.n_pairs * A.npw * A.band_h;
   const int wmax = tw - PS / 2, hmax = A.height + 2 * A.pad - PS / 2;
@@ -825,6 +826,7 @@ constexpr int kConvMin = 12;      // passes; >= kN1 = never
 constexpr float kEarlyStep = 0.3f;   // px; measured on the bench workload: 0.1 ... 1 equivalent (+1 %), below 0.03 the stragglers take over
 constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
 constexpr int kStragWarps = 4;
+constexpr long long kYieldGraceCycles = 20000;   // ~10 us: the walk's blocks announce themselves within a few us of their launch
 template <int PS, int SG, bool FAST>
 __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArgs A) {
   using G = Geom<PS, SG>;
@@ -856,6 +858,11 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
         // no more than what has been appended: a warp does not sit on empty slots while hand-offs trickle in
         if (claimed < cnt) { nclaim = min(G::G, cnt - claimed); base = atomicAdd(ctl + 1, nclaim); break; }
         if (done) break;                                     // nothing left and nothing more to come
+        // Never hold a block slot the walk still needs: had this kernel been scheduled ahead of the walk (the order
+        // of two streams is not guaranteed) it would wait for hand-offs of a walk that cannot become resident.  An
+        // idle warp therefore leaves while the walk is not fully resident; what it leaves behind is picked up by
+        // the sweep launch that follows the walk in stream order (launch_ps).
+        if (ld_volatile(ctl + 3) < A.walk_grid && clock64() - t_start > kYieldGraceCycles) break;
         __nanosleep(400);
         if (clock64() - t_start > 20000000000ll) {           // safety net (~10 s): never spin forever; the host reports it
           if (A.counters) atomicExch(&A.counters[15], 1ull);
@@ -990,6 +997,7 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   const long long want = (total + kWarps * 32 - 1) / (kWarps * 32);
   const long long slots = (148 * walk_blocks(PS, WSG) + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
   const unsigned blocks = (unsigned)(want < slots ? want : slots);
+  a.walk_grid = (int)blocks;
   int n = 2;
   {   // Small launches are bound by the serial miss chains of their few restless patches, not by throughput:
       // hand those to k_stragglers (one pass every ~0.6 us, template and taps on chip) after fewer misses.
@@ -1062,8 +1070,13 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   }
   if (ev) cudaEventRecord(ev[2], s);
   if (a.stragglers) {
-    if (overlap) cudaStreamWaitEvent(s, side->join, 0);
-    else strag(148 * DIS_STRAG_BLOCKS, s);
+    if (overlap) {
+      // Sweep: in stream order behind the walk and its "finished" flag, so it cannot wait on anything.  It finds
+      // nothing to claim unless the side launch yielded (see k_stragglers) and then finishes the list.
+      cudaStreamWaitEvent(s, side->join, 0);
+      strag(148 * DIS_STRAG_BLOCKS, s);
+      ++n;
+    } else strag(148 * DIS_STRAG_BLOCKS, s);
     ++n;
   }
   if (ev) cudaEventRecord(ev[3], s);
