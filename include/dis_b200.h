@@ -84,6 +84,10 @@ typedef struct dis_stats {
 DIS_API void dis_default_params(dis_params* p);
 DIS_API const char* dis_last_error(void);
 DIS_API const char* dis_version(void);
+/* Development entry point (tests, sweeps): the scheduling knobs of DESIGN.md (DIS_OUT_SLICES, DIS_HANDOFF, ...) are
+ * read from the environment once per process; this sets one and re-reads them.  value == NULL removes the override.
+ * No knob changes results.  No counterpart in the reference. */
+DIS_API int dis_tune(const char* name, const char* value);
 
 /* Handle life cycle.  `device` is a CUDA ordinal. */
 DIS_API int dis_create(const dis_params* p, int device, dis_engine** out);

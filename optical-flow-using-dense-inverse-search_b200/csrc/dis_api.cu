@@ -87,6 +87,7 @@ struct dis_engine {
 
   DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers, stage, walk;
   size_t walk_patches = 0;              // capacity of `walk` in patches (largest level x pairs)
+  size_t walk_pair_patches = 0;         // patches of the largest level of one pair (rounded up to 8)
   int straggler_cap = 0;
   dis::LevelPlanes planes[16];          // by absolute scale
   size_t plane_elems[16];
@@ -189,7 +190,10 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
     e->straggler_stride = (64 + (size_t)e->straggler_cap * dis::kStragglerBytes + 255) & ~(size_t)255;
     if (e->stragglers.ensure(kMaxGroups * e->straggler_stride)) return fail(DIS_ERR_ALLOC, "cudaMalloc(stragglers) failed");
     // hand-off between the two phases of a level: 32-byte records first, then the seed entries
-    e->walk_patches = (maxp + 7) & ~(size_t)7;
+    size_t maxnp = 0;
+    for (const Level& L : e->levels) maxnp = std::max(maxnp, (size_t)L.info.num_patches);
+    e->walk_pair_patches = (maxnp + 7) & ~(size_t)7;
+    e->walk_patches = e->walk_pair_patches * n_pairs;
     if (e->walk.ensure(e->walk_patches * dis::kWalkBytesPerPatch)) return fail(DIS_ERR_ALLOC, "cudaMalloc(walk hand-off) failed");
   }
   return DIS_OK;
@@ -220,10 +224,12 @@ dis::SearchArgs level_search_args(dis_engine* e, int g, int s, int p0, int p1) {
   a.work_counter = reinterpret_cast<int*>(sbase) + 8;
   a.stragglers = sbase + 64;
   a.straggler_cap = e->straggler_cap;
-  a.walk_state = e->walk.as<char>() + 32 * (size_t)I.num_patches * p0;
-  a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * I.num_patches * p0;
+  // Regions are per PAIR at the size of the largest level, so that groups of pairs that work on different levels at
+  // the same time (concurrent streams) never share hand-off records.
+  a.walk_state = e->walk.as<char>() + 32 * e->walk_pair_patches * p0;
+  a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * e->walk_pair_patches * p0;
   a.n_pairs = p1 - p0;
-  a.share = getenv("DIS_SHARE") ? e->n_groups : 1;   // full-size grids: a later group fills the SMs an earlier group's tail leaves idle
+  a.share = dis::tuning().share ? e->n_groups : 1;   // full-size grids: a later group fills the SMs an earlier group's tail leaves idle
   a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
   a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
   a.warps_per_pair = (I.num_patches + 31) / 32;
@@ -263,14 +269,14 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st, floa
     if (s == 0 && host_out) {
       // DIS_OUT_SLICES: a count (equal slices) or a comma list of weights, e.g. "4,3,2,1": the last slice's
       // copy is the only one nothing hides, so a tapering split shortens the exposed tail.
-      static const char* env = getenv("DIS_OUT_SLICES");
+      const dis::Tuning& tn = dis::tuning();
       std::vector<double> wt;
-      if (env && strchr(env, ',')) {
-        for (const char* q = env; q && *q; q = strchr(q, ',') ? strchr(q, ',') + 1 : nullptr) wt.push_back(std::max(0.0, atof(q)));
-      } else if (!env && p1 - p0 >= 32) {
+      if (tn.out_slices_nw > 0) {
+        wt.assign(tn.out_slices_w, tn.out_slices_w + tn.out_slices_nw);
+      } else if (tn.out_slices_n < 0 && p1 - p0 >= 32) {
         wt = {3.0, 1.0};   // measured on the 49-pair sequence (profiles/r1k_e2e_slices.log): every further slice costs a launch tail
       } else {
-        const int n = env ? atoi(env) : (p1 - p0 >= 8 ? 2 : 1);
+        const int n = tn.out_slices_n >= 0 ? tn.out_slices_n : (p1 - p0 >= 8 ? 2 : 1);
         wt.assign(std::max(1, std::min(n, p1 - p0)), 1.0);
       }
       double tot = 0, run = 0;
@@ -326,7 +332,7 @@ int run_levels(dis_engine* e, float* host_out = nullptr) {
   if (!e->fork_ev) CU(cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming));
   e->n_groups = G;
   e->search_launches = nl;
-  if (host_out && (G > 1 || e->n_pairs < 8 || (getenv("DIS_OUT_SLICES") && atoi(getenv("DIS_OUT_SLICES")) <= 1))) host_out = nullptr;
+  if (host_out && (G > 1 || e->n_pairs < 8 || (dis::tuning().out_slices_nw == 0 && dis::tuning().out_slices_n >= 0 && dis::tuning().out_slices_n <= 1))) host_out = nullptr;
   if (host_out && !e->copy_stream) CU(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
   if (host_out && e->out.ensure(sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
   e->out_sent = host_out != nullptr;
@@ -415,7 +421,14 @@ void dis_default_params(dis_params* p) {   // src/main.cpp:63-72
 }
 
 const char* dis_last_error(void) { return g_err.c_str(); }
-const char* dis_version(void) { return "dis_b200 0.1 (sm_100a)"; }
+const char* dis_version(void) { return "dis_b200 0.2 (sm_100a)"; }
+
+int dis_tune(const char* name, const char* value) {
+  if (!name || strncmp(name, "DIS_", 4) != 0) return fail(DIS_ERR_PARAM, "dis_tune: knob names start with DIS_");
+  if (value) setenv(name, value, 1); else unsetenv(name);
+  dis::reparse_tuning();
+  return DIS_OK;
+}
 
 int dis_create(const dis_params* p, int device, dis_engine** out) {
   if (!p || !out) return fail(DIS_ERR_PARAM, "null argument");
@@ -435,10 +448,10 @@ int dis_create(const dis_params* p, int device, dis_engine** out) {
   e->prm = *p; e->device = device;
   e->steps = p->steps > 0 ? p->steps : steps_of(p->patch_size, p->patch_overlap);
   e->outlier = p->outlier_thresh > 0.f ? p->outlier_thresh : (float)p->patch_size / 2;   // src/optical_flow.cpp:34
-  if (const char* g = getenv("DIS_GROUPS")) e->max_groups = std::max(1, atoi(g));
+  e->max_groups = dis::tuning().groups;
   {
-    const char* sb = getenv("DIS_SIDE_BLOCKS");          // 0 = run k_stragglers after the walk instead of beside it
-    e->side.blocks = sb ? (unsigned)std::max(0, atoi(sb)) : 592u;
+    // k_stragglers beside the walk: side_blocks blocks per SM (0 = after the walk instead)
+    e->side.blocks = (unsigned)(dis::tuning().side_blocks * prop.multiProcessorCount);
     if (e->side.blocks > 0 &&
         (cudaStreamCreateWithFlags(&e->side.stream, cudaStreamNonBlocking) != cudaSuccess ||
          cudaEventCreateWithFlags(&e->side.fork, cudaEventDisableTiming) != cudaSuccess ||

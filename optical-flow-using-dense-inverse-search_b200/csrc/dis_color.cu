@@ -80,7 +80,7 @@ int launch_color_code(const float* flow, size_t n_pixels, float maxmotion, unsig
   int n = 0;
   if (!(maxmotion > 0.f)) {
     cudaMemsetAsync(scratch, 0, sizeof(unsigned), s);
-    const unsigned blocks = (unsigned)((n_pixels + 255) / 256 < 148 * 8 ? (n_pixels + 255) / 256 : 148 * 8);
+    const unsigned blocks = (unsigned)((n_pixels + 255) / 256 < (size_t)sm_count() * 8 ? (n_pixels + 255) / 256 : (size_t)sm_count() * 8);
     k_flow_maxsq<<<blocks ? blocks : 1, 256, 0, s>>>(reinterpret_cast<const float2*>(flow), n_pixels, scratch);
     ++n;
   }

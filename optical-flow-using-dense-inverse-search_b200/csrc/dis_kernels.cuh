@@ -60,6 +60,7 @@ struct SearchArgs {
   int conv_min;             // k_converge: a warp's batch may leave after this many passes once each of its patches has re-sampled a seen position
   float early_step;         // k_converge -> k_stragglers when the last passes still move by this much (px); 0 = never (set by the launcher)
   int tile_margin;          // ceil(outlierthresh) + 1: how far (px) a tap base can move from the start position's before a reset
+  float one;                // 1.0f, set by the launcher: a run-time constant that keeps ptxas from contracting packed mul + add (dis_search.cu)
 };
 
 struct DensifyArgs {
@@ -68,6 +69,29 @@ struct DensifyArgs {
   size_t dense_stride;      // floats per pair
   int n_pairs, width, height, npw, nph, offw, offh, steps, np, ps;
 };
+
+// Development knobs, read from the environment ONCE per process (first use) and never in launch code.  The defaults
+// are the measured optimum for the bench workload and within a few per cent of it for the other content types of
+// tools/bench_configs.py; none of them changes results.
+struct Tuning {
+  int handoff[4];        // DIS_HANDOFF=a,b,c,d   walk -> k_stragglers after this many misses, by launch size class
+  int walk[12];          // DIS_WALK_TUNE=c,m,a:...  per size class: chunks per round, lanes that must still run, service ageing
+  int conv_min;          // DIS_CONV_MIN          k_converge: earliest pass at which a settled batch may leave
+  int conv_slack;        // DIS_CONV_SLACK        ... with at most this many unsettled patches
+  float early_step;      // DIS_EARLY_STEP        k_converge -> k_stragglers when the last passes still move by this much (px)
+  long long strag_wide;  // DIS_STRAG_WIDE        launches below this many patches use 8 lanes per straggler
+  int share;             // DIS_SHARE             concurrent pair groups size their persistent grids to 1/groups of the GPU
+  int groups;            // DIS_GROUPS            pair groups on concurrent streams (default 1)
+  int side_blocks;       // DIS_SIDE_BLOCKS       blocks per SM of the k_stragglers launch that runs beside the walk (0: after it)
+  int out_slices_n;      // DIS_OUT_SLICES=n or w1,w2,...   slices of the finest level in host-buffer calls (-1: default)
+  double out_slices_w[16];
+  int out_slices_nw;
+};
+const Tuning& tuning();
+void reparse_tuning();   // after the environment changed (dis_tune, a development entry point)
+int current_device();
+// multiProcessorCount of the current device (cached per device)
+int sm_count();
 
 #ifndef DIS_SLOTS
 #define DIS_SLOTS 16

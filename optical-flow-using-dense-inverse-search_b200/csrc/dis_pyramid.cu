@@ -122,13 +122,13 @@ __global__ void __launch_bounds__(256) k_deinterleave(const float2* __restrict__
 }  // namespace
 
 int launch_interleave(const float* dx, const float* dy, float* gxy, size_t n, cudaStream_t s) {
-  const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  const unsigned blocks = (unsigned)((n + 255) / 256 < (size_t)sm_count() * 8 ? (n + 255) / 256 : (size_t)sm_count() * 8);
   k_interleave<<<blocks, 256, 0, s>>>(dx, dy, reinterpret_cast<float2*>(gxy), n);
   return 1;
 }
 
 int launch_deinterleave(const float* gxy, float* dx, float* dy, size_t n, cudaStream_t s) {
-  const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  const unsigned blocks = (unsigned)((n + 255) / 256 < (size_t)sm_count() * 8 ? (n + 255) / 256 : (size_t)sm_count() * 8);
   k_deinterleave<<<blocks, 256, 0, s>>>(reinterpret_cast<const float2*>(gxy), dx, dy, n);
   return 1;
 }

@@ -36,6 +36,8 @@
 //  warp-specialised walker/sampler blocks with a shared-memory request queue; DESIGN.md has the numbers.)
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
+#include <type_traits>
 
 #include "dis_kernels.cuh"
 
@@ -62,6 +64,9 @@ __device__ __forceinline__ const uint4* slot_ptr32(const uint4* cache, unsigned 
 }
 // XOR distance, in slot index space, between way 0 and way w of a set (way bit 0 = bit 1 of y, bits 1.. = bits 1.. of x)
 __host__ __device__ constexpr int way_xor(int w) { return ((w & 1) << 1) | ((w >> 1) << 3); }
+#ifndef DIS_PACKED
+#define DIS_PACKED 1      // packed fp32x2 arithmetic in the sampling code of k_converge / k_stragglers (ps 8)
+#endif
 #ifndef DIS_CHUNK
 #define DIS_CHUNK 6
 #endif
@@ -193,7 +198,18 @@ __device__ __forceinline__ void load_template(const float2* __restrict__ gxy, in
                                               const int (&eoff)[Geom<PS, SG>::NPL],
                                               float2 (&T)[Geom<PS, SG>::NPL]) {
   using G = Geom<PS, SG>;
-  if (PS == 8) {
+  if (PS == 8 && SG == 4 && DIS_PACKED) {
+    // 32-bit loads: the packed arithmetic pairs gx of the lane's two columns (Template8P), and a 64-bit load would tie
+    // gx to gy in a register pair, which ptxas then re-packs with two moves per use on every pass
+    const float* col = reinterpret_cast<const float*>(gxy + c + (sl - 4) - 4 * tw);
+#pragma unroll
+    for (int h = 0; h < G::H; ++h)
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        T[8 * h + r].x = __ldg(col + 2 * (4 * h + r * tw));
+        T[8 * h + r].y = __ldg(col + 2 * (4 * h + r * tw) + 1);
+      }
+  } else if (PS == 8) {
     const float2* col = gxy + c + (sl - 4) - 4 * tw;
 #pragma unroll
     for (int h = 0; h < G::H; ++h)
@@ -323,6 +339,96 @@ __device__ __forceinline__ float2 sample_window8(const Window8<SG>& Wn, float op
     for (int r = 0; r < 8; ++r)
       v[8 * h + r] = ((w3 * Wn.t1[h][r + 1] + w2 * Wn.t0[h][r + 1]) + w1 * Wn.t1[h][r]) + w0 * Wn.t0[h][r];
   return normalise_and_project<8, SG>(v, patnorm, T);
+}
+
+// ---- packed fp32 arithmetic -------------------------------------------------------------------------------------
+// sm_100a has packed fp32 instructions (PTX mul/fma.rn.f32x2, SASS FMUL2 / FFMA2): two IEEE round-to-nearest fp32
+// operations on a 64-bit register pair in ONE issue slot (the FP32 pipe is busy two cycles, so the flop rate is that
+// of the scalar forms; what is saved is instruction issue, which is what bounds these kernels:
+// tools/micro/f32x2_probe.cu).  Each half is bit-identical to the scalar operation — PROVIDED nothing is contracted:
+// ptxas 12.9 fuses mul.rn.f32x2 + add.rn.f32x2 into one FFMA2 in spite of the explicit rounding modifiers and of
+// --fmad=false (it honours both for scalar code), and it also sees through fma(a, 1.0, b) and fma(a, b, -0.0).  So
+// every packed addition is written fma(a, ONE, b) with ONE = {1.0f, 1.0f} read from the kernel arguments (opaque to
+// ptxas): a * 1 is exact, the sum is rounded once, and an FFMA2 can be contracted with nothing.  The SASS of a build
+// must show FMUL2 : FFMA2 = 48 : 53 per sample (checked by tests/test_abi.py::test_packed_arithmetic_is_not_contracted).
+// ps 8 with 4 lanes per patch pairs the lane's two columns (elements r and 8 + r of the lane), which is also the
+// split of Eigen's two SSE packets in tree_sum.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ float lo2(f32x2 a) { float l, h; asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a)); return l; }
+__device__ __forceinline__ float hi2(f32x2 a) { float l, h; asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a)); return h; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b, f32x2 one) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(one), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
+// Eigen redux of the 64 values held as 8 pairs {v[r], v[8 + r]} by the 4 lanes of a sub-group: identical to
+// tree_sum<8, 4> (serial over each packet's 8 values, packet 0 + packet 1, then xor-shuffles 2, 1).
+__device__ __forceinline__ float tree_sum_p(const f32x2 (&v)[8], f32x2 one) {
+  f32x2 s = v[0];
+#pragma unroll
+  for (int r = 1; r < 8; ++r) s = add2(s, v[r], one);
+  float acc = lo2(s) + hi2(s);
+  acc = acc + __shfl_xor_sync(kFull, acc, 2);
+  acc = acc + __shfl_xor_sync(kFull, acc, 1);
+  return acc;
+}
+
+// Template gradients of a ps-8 patch in packed form: x[r] = {gx[r], gx[8 + r]}, y[r] likewise.
+struct Template8P {
+  f32x2 x[8], y[8];
+  __device__ __forceinline__ void set(const float2 (&T)[16]) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      x[r] = pk2(T[r].x, T[8 + r].x); y[r] = pk2(T[r].y, T[8 + r].y);
+      // pin the pairs in registers: without this the compiler keeps the (gx, gy) layout of the loads alive and
+      // re-packs the operands with two moves per multiplication on every pass
+      asm volatile("" : "+l"(x[r]), "+l"(y[r]));
+    }
+  }
+};
+
+// Window8<4> with the taps of the lane's two columns paired: t0[r] = {tap(col - 1, r) of column sl, of column sl + 4}.
+struct Window8P {
+  f32x2 t0[9], t1[9];
+  int bx, by;
+  __device__ __forceinline__ void load_tile(const float* w0, int stride, int sl, int bxi, int byi) {
+    bx = bxi; by = byi;
+#pragma unroll
+    for (int r = 0; r < 9; ++r) {
+      t0[r] = pk2(w0[r * stride + sl], w0[r * stride + sl + 4]);
+      t1[r] = pk2(w0[r * stride + sl + 1], w0[r * stride + sl + 5]);
+    }
+  }
+  __device__ __forceinline__ void load(const float* __restrict__ imB, int tw, int sl, int bxi, int byi) {
+    bx = bxi; by = byi;
+    const float* col = imB + byi * tw + bxi + (sl - 4) - 5 * tw;
+#pragma unroll
+    for (int r = 0; r < 9; ++r) {
+      t0[r] = pk2(__ldg(col + r * tw - 1), __ldg(col + r * tw + 3));
+      t1[r] = pk2(__ldg(col + r * tw), __ldg(col + r * tw + 4));
+    }
+  }
+};
+
+// sample_window8<4> + normalise_and_project<8, 4> on pairs: same operations, same order, half the instructions.
+__device__ __forceinline__ float2 sample_window8p(const Window8P& Wn, float opx, float opy, int patnorm, const Template8P& T, float onef) {
+  const float fl = floorf(opx), fk = floorf(opy);
+  const float a = opx - fl, b = opy - fk;
+  const float w0 = (1 - a) * (1 - b), w1 = a * (1 - b), w2 = b * (1 - a), w3 = a * b;
+  const f32x2 W0 = pk2(w0, w0), W1 = pk2(w1, w1), W2 = pk2(w2, w2), W3 = pk2(w3, w3), one = pk2(onef, onef);
+  f32x2 v[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r)
+    v[r] = add2(add2(add2(mul2(W3, Wn.t1[r + 1]), mul2(W2, Wn.t0[r + 1]), one), mul2(W1, Wn.t1[r]), one), mul2(W0, Wn.t0[r]), one);
+  if (patnorm) {
+    const float nm = -(tree_sum_p(v, one) * (1.0f / 64.0f));   // v - mean == v + (-mean) bit for bit
+    const f32x2 NM = pk2(nm, nm);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) v[r] = add2(v[r], NM, one);
+  }
+  f32x2 px[8], py[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) { px[r] = mul2(T.x[r], v[r]); py[r] = mul2(T.y[r], v[r]); }
+  return make_float2(tree_sum_p(px, one), tree_sum_p(py, one));
 }
 
 // The reset test of src/patch.cpp:185-194 (plus NaN => reset).
@@ -480,8 +586,11 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
       fix_singular(h00, h.y, h11);
       lu.factor(h00, h.y, h11);
     }
-    Window8<SG> Wn;
+    constexpr bool kPacked = DIS_PACKED && PS == 8 && SG == 4;
+    typename std::conditional<kPacked, Window8P, Window8<SG>>::type Wn;
     Wn.bx = -1; Wn.by = -1;
+    Template8P Tp;
+    if constexpr (kPacked) Tp.set(T);
     int k = 0;
     unsigned ns = 0, fifo = 0;
     float moved = 0.f;                                        // largest |delta u| component of the last three passes
@@ -502,7 +611,8 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
       if constexpr (PS == 8) {
         const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
         if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) Wn.load(imB, tw, sl, tb.x, tb.y);
-        sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
+        if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Tp, A.one);
+        else sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
       }
@@ -879,7 +989,10 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
         if (ld_volatile(&list[base + sub < A.straggler_cap ? base + sub : 0].k) >= 0 && base + sub < A.straggler_cap) { have = true; break; }
         if (ld_volatile(ctl + 2) && base + sub >= min(ld_volatile(ctl), A.straggler_cap)) break;   // walk finished: the slot stays empty
         __nanosleep(200);
-        if (clock64() - t_start > 20000000000ll) break;
+        if (clock64() - t_start > 20000000000ll) {           // same safety net: the patch would be lost, so the host must know
+          if (A.counters) atomicExch(&A.counters[15], 1ull);
+          break;
+        }
       }
       __threadfence();
     }
@@ -922,8 +1035,11 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
     int k = e.k;
     bool active = have;
     unsigned was_reset = 0, ns = 0;
-    Window8<SG> Wn;
+    constexpr bool kPacked = DIS_PACKED && PS == 8 && SG == 4;
+    typename std::conditional<kPacked, Window8P, Window8<SG>>::type Wn;
     Wn.bx = -1; Wn.by = -1;
+    Template8P Tp;
+    if constexpr (kPacked) Tp.set(T);
     int ox = 0, oy = 0;
     if (PS == 8 && use_tile) {
       const int2 tb0 = tap_base<PS>(stx, sty, A.pad, wmax, hmax);
@@ -947,7 +1063,8 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
             Wn.load_tile(tile + ry * kTileStride + rx, kTileStride, sl, tb.x, tb.y);
           } else Wn.load(imB, tw, sl, tb.x, tb.y);
         }
-        sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
+        if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Tp, A.one);
+        else sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
       }
@@ -987,54 +1104,54 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
 template <int PS, int SG, bool FAST>
 int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const SearchSide* side) {
   SearchArgs a = a_in;
+  a.one = 1.0f;
   constexpr int WSG = (DIS_WALK_SG8 && PS == 8) ? 8 : SG;   // sub-group size of the walk phase's (rare) service rounds
   const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
-  cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  static bool attr_done[64] = {false};                        // per template instantiation and device
+  const int dev = current_device();
+  const bool set_attr = !attr_done[dev];
+  attr_done[dev] = true;
+  if (set_attr) {
+    cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_inverse_search<PS, WSG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    constexpr int WS = PS == 8 ? 8 : SG;
+    const size_t tsm_w = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, WS>::G * kTile * kTileStride : 0;
+    cudaFuncSetAttribute(k_stragglers<PS, WS, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm_w);
+    cudaFuncSetAttribute(k_stragglers<PS, WS, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    const size_t tsm_n = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SG>::G * kTile * kTileStride : 0;
+    cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm_n);
+    cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  }
   // persistent warps: lanes fetch patches from a global counter until the level is done
   if (a.band_h <= 0) { a.band_y0 = 0; a.band_h = a.nph; }
   const long long total = (long long)a.n_pairs * a.npw * a.band_h;
   const long long want = (total + kWarps * 32 - 1) / (kWarps * 32);
-  const long long slots = (148 * walk_blocks(PS, WSG) + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
+  const int n_sm = sm_count();
+  const Tuning& tn = tuning();
+  const long long slots = ((long long)n_sm * walk_blocks(PS, WSG) + (a.share > 1 ? a.share : 1) - 1) / (a.share > 1 ? a.share : 1);
   const unsigned blocks = (unsigned)(want < slots ? want : slots);
   a.walk_grid = (int)blocks;
   int n = 2;
   {   // Small launches are bound by the serial miss chains of their few restless patches, not by throughput:
       // hand those to k_stragglers (one pass every ~0.6 us, template and taps on chip) after fewer misses.
-    static const char* env = getenv("DIS_HANDOFF");
-    int t0 = 24, t1 = 48, t2 = 128, t3 = 384;
-    if (env) sscanf(env, "%d,%d,%d,%d", &t0, &t1, &t2, &t3);
-    a.handoff_misses = total < 200000 ? t0 : total < 600000 ? t1 : total < 2000000 ? t2 : t3;
-    {   // per size class: chunks per round, lanes that must still run to go on, service ageing
-      static const char* env_t = getenv("DIS_WALK_TUNE");
-      int t[12] = {10, 24, DIS_AGE, 10, 24, DIS_AGE, 10, 24, DIS_AGE, 10, 24, DIS_AGE};   // measured: tools/sweep2.sh, DESIGN.md 3.2
-      if (env_t) sscanf(env_t, "%d,%d,%d:%d,%d,%d:%d,%d,%d:%d,%d,%d", t, t + 1, t + 2, t + 3, t + 4, t + 5, t + 6, t + 7, t + 8, t + 9, t + 10, t + 11);
-      const int c = total < 200000 ? 0 : total < 600000 ? 1 : total < 2000000 ? 2 : 3;
-      a.walk_chunks = t[3 * c]; a.walk_minrun = t[3 * c + 1]; a.walk_age = t[3 * c + 2];
-    }
-    static const char* env_c = getenv("DIS_CONV_MIN");
-    a.conv_min = env_c ? atoi(env_c) : kConvMin;
-    static const char* env_s = getenv("DIS_CONV_SLACK");
-    a.conv_slack = env_s ? atoi(env_s) : 2;
-    static const char* env_e = getenv("DIS_EARLY_STEP");
-    a.early_step = env_e ? (float)atof(env_e) : kEarlyStep;
+    const int c = total < 200000 ? 0 : total < 600000 ? 1 : total < 2000000 ? 2 : 3;   // size class of the launch
+    a.handoff_misses = tn.handoff[c];
+    a.walk_chunks = tn.walk[3 * c]; a.walk_minrun = tn.walk[3 * c + 1]; a.walk_age = tn.walk[3 * c + 2];
+    a.conv_min = tn.conv_min;
+    a.conv_slack = tn.conv_slack;
+    a.early_step = tn.early_step;
   }
   // k_stragglers: 4 lanes per patch (ps 8) have the fewest instructions per sample; 8 lanes per patch have the
   // shorter dependent chain per pass, which is what bounds a small launch (its last hand-offs run alone).
-  static const char* env_w = getenv("DIS_STRAG_WIDE");
-  const long long wide_below = env_w ? atoll(env_w) : kStragWideBelow;
+  const long long wide_below = tn.strag_wide;
   const bool wide = PS == 8 && SG == 4 && (DIS_STRAG_SG8 || total < wide_below);
   auto strag = [&](unsigned nblocks, cudaStream_t st) {
     if (wide) {
       constexpr int WS = PS == 8 ? 8 : SG;
       const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, WS>::G * kTile * kTileStride : 0;
-      cudaFuncSetAttribute(k_stragglers<PS, WS, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
-      cudaFuncSetAttribute(k_stragglers<PS, WS, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
       k_stragglers<PS, WS, FAST><<<nblocks, kStragWarps * 32, tsm, st>>>(a);
     } else {
       const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SG>::G * kTile * kTileStride : 0;
-      cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm);
-      cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
       k_stragglers<PS, SG, FAST><<<nblocks, kStragWarps * 32, tsm, st>>>(a);
     }
   };
@@ -1050,9 +1167,7 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
   {   // phase 1: G patches per warp, grid-stride over a few waves of resident blocks
     constexpr int kConvWarps = conv_warps(PS);
     const long long cwant = (total + kConvWarps * Geom<PS, SG>::G - 1) / (kConvWarps * Geom<PS, SG>::G);
-    const long long cslots = 148LL * (conv_blocks(PS) > 1 ? conv_blocks(PS) * 4 : 12) / (a.share > 1 ? a.share : 1);
-    // one shared-memory carve-out for all three kernels: kernels with different carve-outs cannot share an SM
-    cudaFuncSetAttribute(k_converge<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    const long long cslots = (long long)n_sm * (conv_blocks(PS) > 1 ? conv_blocks(PS) * 4 : 12) / (a.share > 1 ? a.share : 1);
     k_converge<PS, SG, FAST><<<(unsigned)(cwant < cslots ? cwant : cslots), kConvWarps * 32, 0, s>>>(a);
   }
   if (ev) cudaEventRecord(ev[1], s);
@@ -1074,9 +1189,9 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
       // Sweep: in stream order behind the walk and its "finished" flag, so it cannot wait on anything.  It finds
       // nothing to claim unless the side launch yielded (see k_stragglers) and then finishes the list.
       cudaStreamWaitEvent(s, side->join, 0);
-      strag(148 * DIS_STRAG_BLOCKS, s);
+      strag((unsigned)n_sm * DIS_STRAG_BLOCKS, s);
       ++n;
-    } else strag(148 * DIS_STRAG_BLOCKS, s);
+    } else strag((unsigned)n_sm * DIS_STRAG_BLOCKS, s);
     ++n;
   }
   if (ev) cudaEventRecord(ev[3], s);
@@ -1084,6 +1199,62 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
 }
 
 }  // namespace
+
+namespace {
+Tuning parse_tuning() {
+    Tuning t;
+    const int h[4] = {24, 48, 128, 384};
+    for (int i = 0; i < 4; ++i) t.handoff[i] = h[i];
+    if (const char* e = getenv("DIS_HANDOFF")) sscanf(e, "%d,%d,%d,%d", t.handoff, t.handoff + 1, t.handoff + 2, t.handoff + 3);
+    for (int c = 0; c < 4; ++c) { t.walk[3 * c] = 10; t.walk[3 * c + 1] = 24; t.walk[3 * c + 2] = DIS_AGE; }   // measured: tools/sweep2.sh, DESIGN.md 3.2
+    if (const char* e = getenv("DIS_WALK_TUNE"))
+      sscanf(e, "%d,%d,%d:%d,%d,%d:%d,%d,%d:%d,%d,%d", t.walk, t.walk + 1, t.walk + 2, t.walk + 3, t.walk + 4, t.walk + 5, t.walk + 6,
+             t.walk + 7, t.walk + 8, t.walk + 9, t.walk + 10, t.walk + 11);
+    const char* e;
+    t.conv_min = (e = getenv("DIS_CONV_MIN")) ? atoi(e) : kConvMin;
+    t.conv_slack = (e = getenv("DIS_CONV_SLACK")) ? atoi(e) : 2;
+    t.early_step = (e = getenv("DIS_EARLY_STEP")) ? (float)atof(e) : kEarlyStep;
+    t.strag_wide = (e = getenv("DIS_STRAG_WIDE")) ? atoll(e) : kStragWideBelow;
+    t.share = getenv("DIS_SHARE") ? 1 : 0;
+    t.groups = (e = getenv("DIS_GROUPS")) ? (atoi(e) > 1 ? atoi(e) : 1) : 1;
+    t.side_blocks = (e = getenv("DIS_SIDE_BLOCKS")) ? (atoi(e) > 0 ? atoi(e) : 0) : 4;
+    t.out_slices_n = -1; t.out_slices_nw = 0;
+    if ((e = getenv("DIS_OUT_SLICES"))) {
+      if (strchr(e, ',')) {
+        for (const char* q = e; q && *q && t.out_slices_nw < 16; q = strchr(q, ',') ? strchr(q, ',') + 1 : nullptr) {
+          const double w = atof(q);
+          t.out_slices_w[t.out_slices_nw++] = w > 0 ? w : 0;
+        }
+      } else t.out_slices_n = atoi(e);
+    }
+    return t;
+}
+Tuning g_tuning;
+bool g_tuning_ready = false;
+}  // namespace
+
+const Tuning& tuning() {
+  if (!g_tuning_ready) { g_tuning = parse_tuning(); g_tuning_ready = true; }
+  return g_tuning;
+}
+void reparse_tuning() { g_tuning = parse_tuning(); g_tuning_ready = true; }
+
+int current_device() {
+  int dev = 0;
+  return (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64) ? dev : 0;
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
 
 int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev, const SearchSide* side) {
   const bool fast = a.conv_eps2 > 0.f;

@@ -44,7 +44,7 @@ _lib = None
 
 # every symbol include/dis_b200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
-    "dis_default_params", "dis_last_error", "dis_version", "dis_create", "dis_destroy", "dis_run_pair_u8",
+    "dis_default_params", "dis_last_error", "dis_version", "dis_tune", "dis_create", "dis_destroy", "dis_run_pair_u8",
     "dis_run_batch_u8", "dis_run_sequence_u8", "dis_run_pyramids", "dis_construct_pyramid", "dis_upload_frames_u8",
     "dis_run_resident", "dis_download_flows", "dis_synchronize", "dis_timer_start", "dis_timer_stop_ms",
     "dis_last_search_ms", "dis_last_search_level_ms", "dis_last_search_phase_ms", "dis_num_levels", "dis_get_level_info", "dis_get_patches", "dis_get_level_flow",

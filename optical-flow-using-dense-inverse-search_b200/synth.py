@@ -36,7 +36,7 @@ def _to_u8(a: np.ndarray) -> np.ndarray:
     return np.clip(np.rint(a), 0, 255).astype(np.uint8)
 
 
-def make_pair(w: int = 1024, h: int = 436, seed: int = 0, amp: float | None = None, margin: int = 32):
+def make_pair(w: int = 1024, h: int = 436, seed: int = 0, amp: float | None = None, margin: int = 32, canvas_fn=None):
     """Frame A, frame B (u8, h x w) and the flow A->B (float32 h x w x 2).
 
     B(x + flow(x)) ~= A(x): B is the canvas sampled (bicubic) at x - flow_b where flow_b is the
@@ -47,6 +47,8 @@ def make_pair(w: int = 1024, h: int = 436, seed: int = 0, amp: float | None = No
     if amp is None:
         amp = 3.0 * w / 1024.0
     canvas = texture(h + 2 * margin, w + 2 * margin, rng)
+    if canvas_fn is not None:
+        canvas = canvas_fn(canvas)
     f = gt_flow(h, w, amp)
     y, x = np.mgrid[0:h, 0:w].astype(np.float64)
     a = canvas[margin:margin + h, margin:margin + w]
@@ -55,6 +57,18 @@ def make_pair(w: int = 1024, h: int = 436, seed: int = 0, amp: float | None = No
     fy = ndimage.map_coordinates(f[..., 1], [y - f[..., 1], x - f[..., 0]], order=1, mode="nearest")
     b = ndimage.map_coordinates(canvas, [y - fy + margin, x - fx + margin], order=3, mode="nearest")
     return _to_u8(a), _to_u8(b), f.astype(np.float32)
+
+
+def make_lowtex_pair(w: int = 1024, h: int = 436, seed: int = 0, amp: float | None = None):
+    """make_pair on a canvas whose texture fades out from the middle to the right: the right 40 % of both
+    frames is exactly flat (zero gradients => singular Hessians), the band before it
+    has weak texture (long, badly conditioned iterations)."""
+    def fade(canvas):
+        ww = canvas.shape[1]
+        x = np.arange(ww, dtype=np.float64) / ww
+        m = np.clip((0.6 - x) / 0.2, 0.0, 1.0)          # 1 left of 40 %, 0 right of 60 %
+        return 128.0 + (canvas - 128.0) * m[None, :]
+    return make_pair(w, h, seed=seed, amp=amp, canvas_fn=fade)
 
 
 def make_sequence(n_frames: int = 50, w: int = 1024, h: int = 436, seed: int = 0, margin: int = 176):
