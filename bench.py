@@ -88,57 +88,109 @@ def strip_patches(oracle_obj, w, h):
     return sum((lambda i: i["npw"] * i["nph"])(oracle_obj.level_info(Wp, Hp, s, PS, PS, 0.7)) for s in range(4))
 
 
-def cpu_run(kind: str, threads: int, strip_h: int, seed0: int, reps: int = 1):
-    """Time `threads` concurrent single-threaded oracle runs (one pair each, as the reference is
-    single-threaded) on 1024 x strip_h crops of synthetic pairs.  Returns (equivalent full pairs/s, secs)."""
+_SEQ = {}
+
+
+def bench_sequence(seed: int):
+    """The timed workload: make_sequence(50, 1024, 436, seed) — cached, both arms and the parity check use it."""
     import dis_b200
+    if seed not in _SEQ:
+        _SEQ[seed] = dis_b200.synth.make_sequence(N_FRAMES, W, H, seed=seed)
+    return _SEQ[seed]
+
+
+def cpu_run(kind: str, threads: int, strip_h: int, first_pair: int):
+    """Time `threads` concurrent single-threaded runs of the CPU reference (one pair each, as the reference is
+    single-threaded) on pairs first_pair, first_pair + 1, ... (mod 49) of the timed sequence, optionally cropped
+    to their top strip_h rows.  Returns (equivalent full pairs/s, secs, fraction of a pair one run is)."""
     import oracle
     orc = oracle.Oracle(kind)
+    frames, _ = bench_sequence(100)
     pairs = []
     for t in range(threads):
-        a, b, _ = dis_b200.synth.make_pair(W, H, seed=seed0 + t)
-        pairs.append((np.ascontiguousarray(a[:strip_h]), np.ascontiguousarray(b[:strip_h])))
-    equiv = strip_patches(orc, W, strip_h) / strip_patches(orc, W, H)
-    best = None
-    for _ in range(reps):
-        ths = [threading.Thread(target=orc.run_pair_u8, args=p) for p in pairs]
-        t0 = time.perf_counter()
-        for t in ths: t.start()
-        for t in ths: t.join()
-        dt = time.perf_counter() - t0
-        best = dt if best is None else min(best, dt)
-    return threads * equiv / best, best, equiv
+        i = (first_pair + t) % N_PAIRS
+        pairs.append((np.ascontiguousarray(frames[i][:strip_h]), np.ascontiguousarray(frames[i + 1][:strip_h])))
+    equiv = 1.0 if strip_h >= H else strip_patches(orc, W, strip_h) / strip_patches(orc, W, H)
+    ths = [threading.Thread(target=orc.run_pair_u8, args=p) for p in pairs]
+    t0 = time.perf_counter()
+    for t in ths: t.start()
+    for t in ths: t.join()
+    dt = time.perf_counter() - t0
+    return threads * equiv / dt, dt, equiv
 
 
 def reference_arm(args, rank: int):
-    """--impl reference: the reference's own CPU implementation of the path on the host cores
-    (oracle/_ref = its unmodified engine sources; else the C port), rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores (oracle/_ref = its
+    unmodified engine sources; else the C port), rank 0 only.  Same config as the GPU arm: WHOLE 1024x436 pairs of
+    the same 50-frame sequence, default parameters, max_iter 1000; a step = one pair per host core, all cores busy.
+    CPU code needs no warm-up, so the --warmup steps are not run (recorded in the line); --ref-strip H crops the
+    pairs to their top H rows for a quick look (recorded as same_config: false)."""
     if rank != 0:
         return
     import oracle
     kind = "reference" if oracle.load_ref() is not None else "port"
     cores = os.cpu_count() or 1
-    total_steps = args.steps + args.warmup
-    # bound the run: a full pair costs ~40-60 s per core; choose the strip so all steps fit ~4 min
-    budget = 240.0 / max(1, total_steps)
-    strip_h = 436 if budget >= 70 else 216 if budget >= 35 else 104 if budget >= 18 else 56 if budget >= 9 else 24
-    vals, secs, equiv = [], [], 1.0
-    for s in range(total_steps):
-        v, dt, equiv = cpu_run(kind, cores, strip_h, seed0=1000 + s * cores)
-        if s >= args.warmup:
-            vals.append(v); secs.append(dt)
+    strip_h = args.ref_strip if 0 < args.ref_strip < H else H
+    secs, equiv = [], 1.0
+    for s in range(args.steps):
+        _, dt, equiv = cpu_run(kind, cores, strip_h, first_pair=s * cores)
+        secs.append(dt)
     t = float(np.sum(secs))
     value = cores * equiv * len(secs) / t
-    sample = (f"each step: {cores} concurrent single-threaded runs, one synthetic pair each, cropped to 1024x{strip_h} "
-              f"(= {equiv:.4f} of a 1024x436 pair by patch count), default parameters, max_iter 1000")
+    whole = strip_h >= H
+    sample = (f"each step: {cores} concurrent single-threaded runs, one pair of the timed 50-frame sequence each, "
+              + ("whole 1024x436 pairs" if whole else f"cropped to 1024x{strip_h} (= {equiv:.4f} of a pair by patch count)")
+              + ", default parameters, max_iter 1000; no warm-up steps")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * t / len(secs), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "50-frame synthetic 1024x436 sequence (49 pairs), defaults, sampled", "mode": "exact"},
+            "warmup": 0, "warmup_requested": args.warmup, "ms_per_step": 1e3 * t / len(secs), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "same_config": whole,
+            "config": workload_config(1000), "pairs_per_step_reference": cores if whole else cores * equiv,
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def workload_config(max_iter: int = 1000) -> dict:
+    """`config` of BOTH arms (the driver compares them)."""
+    return {"workload": "50-frame synthetic 1024x436 sequence (49 pairs), defaults (patch 8, scales 3->0, overlap 0.7, mean-norm, max_iter %d)" % max_iter,
+            "mode": "exact (bit-identical to the reference's 1001 passes per patch)", "pairs_per_step_per_gpu": N_PAIRS,
+            "l2": "per-step working set ~0.6 GB (pyramids + flows) exceeds the 126 MB L2; no explicit flush"}
+
+
+def code_sha():
+    """sha256 over the kernel sources: a profile-derived constant (roofline.traffic) is only valid for the code it was
+    captured from."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "optical-flow-using-dense-inverse-search_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh")):
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()
+
+
+def parity_check(flows, pairs=(0, 24, 48)):
+    """Bit-compare flows of the timed sequence (rank 0: seed 100) with the reference-generated goldens
+    (tests/golden/golden_full.npz, made by tests/golden/make_golden_full.py from oracle/_ref).  No oracle code runs."""
+    import hashlib
+    try:
+        z = np.load(os.path.join(ROOT, "tests", "golden", "golden_full.npz"))
+        meta = {m["name"]: m for m in json.loads(str(z["meta"]))}
+    except Exception as ex:  # noqa: BLE001
+        return {"pairs_checked": [], "bit_identical": None, "note": f"goldens unavailable: {ex}"}
+    frames, _ = bench_sequence(100)
+    ok, checked = True, []
+    for i in pairs:
+        m = meta.get(f"bench_seq100_pair{i}")
+        if m is None:
+            continue
+        if hashlib.sha256(np.stack([frames[i], frames[i + 1]]).tobytes()).hexdigest() != m["frames_sha"]:
+            return {"pairs_checked": checked, "bit_identical": None, "note": "synthetic generator drifted: golden inputs not reproducible here"}
+        checked.append(i)
+        ok = ok and hashlib.sha256(np.ascontiguousarray(flows[i]).tobytes()).hexdigest() == m["flow_sha"]
+    return {"pairs_checked": checked, "bit_identical": bool(ok) if checked else None,
+            "against": "tests/golden/golden_full.npz (the reference's own sources, max_iter 1000)"}
 
 
 def main():
@@ -150,6 +202,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fast-mode", action="store_true")
     ap.add_argument("--max-iter", type=int, default=1000)
+    ap.add_argument("--ref-strip", type=int, default=0, help="reference arm: crop pairs to their top H rows (0 = whole pairs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -179,7 +232,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    frames, gt = dis_b200.synth.make_sequence(N_FRAMES, W, H, seed=100 + rank)
+    frames, gt = bench_sequence(100 + rank)
     eng = dis_b200.Engine(local_rank, max_iter=args.max_iter)
     first = np.arange(N_PAIRS, dtype=np.int32)
 
@@ -220,6 +273,12 @@ def main():
     e2e_s = max_over_ranks(e2e_s)
     clocks = sampler.stop() if sampler else None
     checksum = float(np.abs(pin_out.numpy()).mean())
+    # parity of what was just timed: the e2e buffer AND the device-resident result against the reference-generated goldens
+    parity = None
+    if rank == 0 and args.max_iter == 1000:
+        parity = parity_check(pin_out.numpy())
+        res = parity_check(eng.download_flows())
+        parity["resident_run_bit_identical"] = res["bit_identical"]
 
     # ---- informational: the optional convergence early-out (conv_eps > 0), a REPORTED DEVIATION from the
     #      reference (which has no convergence test); never the headline ------------------------
@@ -251,54 +310,71 @@ def main():
         hbm_peak, sm_max, peak_src = measured_peaks()
         value = world * N_PAIRS * args.steps / (dev_ms * 1e-3)
         e2e = world * N_PAIRS * args.steps / e2e_s
-        # Algorithmic HBM bytes per launch, summed over the 4 levels of a step:
-        #  k_converge: the three live padded planes (first.dx, first.dy, second.img), the coarser flow read,
-        #              the 288-byte hand-off record written per patch;
-        #  walk:       the hand-off record read, u (8 B) and the iteration count (4 B) written per patch.
         infos = [eng.level_info(l) for l in range(nl)]
         patches = sum(li["num_patches"] for li in infos) * N_PAIRS
-        alg_conv = sum(N_PAIRS * (3 * 4 * li["tmp_w"] * li["tmp_h"] + 288 * li["num_patches"]
-                                  + (8 * (li["width"] // 2) * (li["height"] // 2) if l < nl - 1 else 0)) for l, li in enumerate(infos))
-        alg_walk = 300 * patches
         conv_ms, walk_ms, strag_ms = (sum(x) for x in phase_ms)
-        achieved = alg_walk / (walk_ms * 1e-3) / 1e9
-        alg = alg_conv + alg_walk
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "r1_walk_traffic.json")   # dram bytes of the walk launches, one ncu --set full capture
-        if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get("dram_bytes_per_step")
+        step_ms = dev_ms / args.steps
         sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
-        issue_peak = 148 * 128 * sm_mhz * 1e6           # fp32 lane-ops/s without FMA at the measured clock
+        n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+        # ---- the roof of this path is fp32 instruction issue WITHOUT FMA, not HBM: executed work =
+        #      sampled passes x (13 ps^2 + 32 = 864 lane-ops) + replayed (memoised) passes x 11 lane-ops, over the time
+        #      the three search kernels of the four levels take; peak = SMs x 128 fp32 lanes x the clock measured live.
+        issue_peak = n_sm * 128 * sm_mhz * 1e6
+        sampled = st["sampled_iterations"]
+        replayed = st["patch_iterations"] - sampled
+        s_conv, s_walk = st["sampled_converge"], st["sampled_walk"]
+        s_strag = sampled - s_conv - s_walk
+        lane_ops = sampled * F_ITER + replayed * 11
+        achieved = lane_ops / (search_ms * 1e-3)
+        # ---- HBM: 26.0 MB compulsory per Sintel pair (inputs once, four live planes written + read
+        #      once, level flows written once and the coarser ones read once)
+        HBM_PER_PAIR = 26.0e6
+        hbm_achieved = HBM_PER_PAIR * N_PAIRS / (step_ms * 1e-3) / 1e9
+        traffic, traffic_note = None, None
+        tpath = os.path.join(ROOT, "profiles", "r2_search_traffic.json")   # dram bytes of the search launches of one step: ncu --set full
+        if os.path.exists(tpath):
+            tj = json.load(open(tpath))
+            if tj.get("code_sha") == code_sha():
+                traffic = tj.get("dram_bytes_per_step")
+            else:
+                traffic_note = "profiles/r2_search_traffic.json was captured from other kernel sources (code_sha differs): not reported"
+        else:
+            traffic_note = "no ncu capture on file for these kernel sources"
         it_rate = st["patch_iterations"] / (search_ms * 1e-3)
-        smp_rate = st["sampled_iterations"] / (search_ms * 1e-3)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "50-frame synthetic 1024x436 sequence (49 pairs), defaults (patch 8, scales 3->0, overlap 0.7, mean-norm, max_iter %d)" % args.max_iter,
-                       "mode": "exact (bit-identical to the reference's 1001 passes per patch)", "pairs_per_step_per_gpu": N_PAIRS,
-                       "l2": "per-step working set ~0.6 GB (pyramids + flows) exceeds the 126 MB L2; no explicit flush"},
+            "config": workload_config(args.max_iter),
             "mpix_per_s": value * W * H / 1e6,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(pin_in.numel()), "d2h_bytes_per_step": int(pin_out.numel() * 4),
                     "api": "dis_run_sequence_u8 (pinned host buffers)", "ms_per_step": 1e3 * e2e_s / args.steps},
             "gpu_launches": int(launches_per_step * args.steps),
-            "roofline": {"kernel": "k_inverse_search<8,8> = the memoised walk (4 launches per step, one per level; figures are per step)",
-                         "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": traffic, "peak_source": peak_src + " (burst figure of MEASURED_PEAKS.json)",
-                         "algorithmic_bytes_per_step": alg_walk, "kernel_ms_per_step": walk_ms,
-                         "kernel_ms_per_level_fine_to_coarse": phase_ms[1],
-                         "note": "issue/latency-bound, not HBM-bound (SURVEY.md §8d, DESIGN.md §3.2): see roofline_issue"},
+            "parity": parity,
+            "roofline": {"kernel": "the inverse search = k_converge + k_inverse_search (memoised walk) + k_stragglers, 4 levels (figures per step)",
+                         "bound": "fp32_issue", "achieved": achieved / 1e12, "peak": issue_peak / 1e12, "unit": "Tlane-op/s (fp32, no FMA)",
+                         "frac": achieved / issue_peak, "traffic": traffic, "traffic_note": traffic_note,
+                         "peak_source": f"{n_sm} SMs x 128 fp32 lanes x {sm_mhz:.0f} MHz (median SM clock sampled during the timed region)",
+                         "executed": {"sampled_passes": sampled, "replayed_passes": replayed, "lane_ops_per_sampled_pass": F_ITER,
+                                      "lane_ops_per_replayed_pass": 11},
+                         "kernel_ms_per_step": search_ms,
+                         "reference_equivalent_frac": it_rate * F_ITER / issue_peak,
+                         "note": "reference_equivalent_frac counts all 1001 passes per patch as if sampled: work skipped by exact memoisation, "
+                                 "NOT a fraction of peak"},
+            "roofline_hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
+                             "algorithmic_bytes_per_pair": HBM_PER_PAIR, "peak_source": peak_src + " (burst figure of MEASURED_PEAKS.json)",
+                             "note": "SURVEY.md 8(d)-i compulsory bytes over the whole step; the path is not HBM-bound"},
             "roofline_kernels": [
-                {"kernel": "k_converge<8,4>", "ms_per_step": conv_ms, "algorithmic_bytes_per_step": alg_conv,
-                 "achieved_gbs": alg_conv / (conv_ms * 1e-3) / 1e9, "frac_hbm": alg_conv / (conv_ms * 1e-3) / 1e9 / hbm_peak,
-                 "fp32_lane_ops_per_s": min(24, args.max_iter + 1) * patches * F_ITER / (conv_ms * 1e-3),
+                {"kernel": "k_converge<8,4>", "ms_per_step": conv_ms, "sampled_passes": s_conv,
+                 "fp32_lane_ops_per_s": s_conv * F_ITER / (conv_ms * 1e-3), "frac_fp32_issue": s_conv * F_ITER / (conv_ms * 1e-3) / issue_peak,
                  "ms_per_level_fine_to_coarse": phase_ms[0]},
-                {"kernel": "k_stragglers<8,4>", "ms_per_step": strag_ms, "ms_per_level_fine_to_coarse": phase_ms[2]}],
-            "roofline_issue": {"unit": "fp32 lane-op/s (no FMA)", "peak": issue_peak, "sm_mhz": sm_mhz,
-                               "reference_equivalent": {"patch_iterations_per_s": it_rate, "frac": it_rate * F_ITER / issue_peak},
-                               "executed": {"sampled_iterations_per_s": smp_rate, "frac": smp_rate * F_ITER / issue_peak},
-                               "tap_bytes_per_s_executed": smp_rate * B_TAP},
-            "stats_per_step": st, "stats_job_per_step": job, "search_share_of_step": search_ms / (dev_ms / args.steps),
+                {"kernel": "k_inverse_search<8,8> (walk)", "ms_per_step": walk_ms, "sampled_passes": s_walk, "replayed_passes": replayed,
+                 "fp32_lane_ops_per_s": (s_walk * F_ITER + replayed * 11) / (walk_ms * 1e-3),
+                 "frac_fp32_issue": (s_walk * F_ITER + replayed * 11) / (walk_ms * 1e-3) / issue_peak,
+                 "ms_per_level_fine_to_coarse": phase_ms[1]},
+                {"kernel": "k_stragglers<8,4>", "ms_per_step_not_hidden_by_the_walk": strag_ms, "sampled_passes": s_strag,
+                 "ms_per_level_fine_to_coarse": phase_ms[2]}],
+            "stats_per_step": st, "stats_job_per_step": job, "search_share_of_step": search_ms / step_ms,
             "clocks": clocks, "checksum": checksum,
         }
         if fast is not None:
@@ -306,10 +382,10 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             import oracle
             kind = "reference" if oracle.load_ref() is not None else "port"
-            v, dt, equiv = cpu_run(kind, 1, 216, seed0=100)
+            v, dt, equiv = cpu_run(kind, 1, 216, first_pair=0)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": kind,
-                                    "sample": f"one synthetic pair cropped to 1024x216 (= {equiv:.4f} of a 1024x436 pair by patch count), "
-                                              f"single thread, {dt:.1f} s"}
+                                    "sample": f"pair 0 of the timed sequence cropped to 1024x216 (= {equiv:.4f} of a 1024x436 pair by patch count), "
+                                              f"single thread, {dt:.1f} s; --impl reference times whole pairs on all cores"}
         print(json.dumps(line), flush=True)
     eng.close()
     if dist is not None:

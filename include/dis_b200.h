@@ -78,7 +78,8 @@ typedef struct dis_stats {
   unsigned long long resets;            /* patches reset to their initial u (src/patch.cpp:185-194) */
   unsigned long long start_oob;         /* patches whose start was out of bounds (src/patch.cpp:131-138) */
   unsigned long long kernel_launches;   /* kernels launched by the last run */
-  unsigned long long reserved[2];
+  unsigned long long sampled_converge;  /* of sampled_iterations: those of k_converge (the first passes of every patch) ... */
+  unsigned long long sampled_walk;      /* ... and of the memoised walk; the remainder ran in k_stragglers */
 } dis_stats;
 
 DIS_API void dis_default_params(dis_params* p);
@@ -215,7 +216,11 @@ DIS_API int dis_tiled_finish(dis_engine* e, float* flow_out);
  * (called at src/main.cpp:200-201 with maxmotion = -1: the range is the field's own maximum).
  * flow: h x w x 2 fp32 host; bgr_out: h x w x 3 u8 host (B,G,R as cv::Mat CV_8UC3). */
 DIS_API int dis_color_code(dis_engine* e, const float* flow, int w, int h, float maxmotion, uint8_t* bgr_out);
-/* Same for the (device-resident) cropped flow of pair `pair` of the last run. */
+/* Same for the (device-resident) cropped flow of pair `pair` of the last run.
+ * NOTE "last run": dis_run_batch_u8 / dis_run_sequence_u8 work in chunks of at most 128 pairs; after a longer call
+ * the device holds only the LAST chunk, and `pair` (here, in dis_get_patches and in dis_get_level_flow) indexes that
+ * chunk: pair 0 is pair 128 * floor((n_pairs - 1) / 128) of the call.  Colour a long sequence from the host flows
+ * with dis_color_code (tools/dis_sequence.cpp does). */
 DIS_API int dis_color_code_pair(dis_engine* e, int pair, float maxmotion, uint8_t* bgr_out);
 
 #ifdef __cplusplus

@@ -181,7 +181,7 @@ int setup_run(dis_engine* e, int W, int H, int pad, int n_frames, int n_pairs) {
       return fail(DIS_ERR_ALLOC, "cudaMalloc(level buffers) failed");
   }
   if (e->pairs.ensure(sizeof(int2) * (size_t)n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(pairs) failed");
-  if (e->counters.ensure(sizeof(unsigned long long) * 16)) return fail(DIS_ERR_ALLOC, "cudaMalloc(counters) failed");
+  if (e->counters.ensure(sizeof(unsigned long long) * dis::kCounters)) return fail(DIS_ERR_ALLOC, "cudaMalloc(counters) failed");
   // hand-off list of the inverse search (20 bytes per entry + the counter in front)
   {
     size_t maxp = 0;
@@ -229,6 +229,7 @@ dis::SearchArgs level_search_args(dis_engine* e, int g, int s, int p0, int p1) {
   a.walk_state = e->walk.as<char>() + 32 * e->walk_pair_patches * p0;
   a.walk_seeds = e->walk.as<char>() + 32 * e->walk_patches + 16 * (size_t)dis::kWalkSeeds * e->walk_pair_patches * p0;
   a.n_pairs = p1 - p0;
+  a.walk_capacity = (long long)e->walk_pair_patches * (e->n_pairs - p0);
   a.share = dis::tuning().share ? e->n_groups : 1;   // full-size grids: a later group fills the SMs an earlier group's tail leaves idle
   a.width = I.width; a.height = I.height; a.pad = e->pad; a.tmp_w = I.tmp_w;
   a.npw = I.npw; a.nph = I.nph; a.offw = I.offw; a.offh = I.offh; a.steps = I.steps; a.np = I.num_patches;
@@ -318,7 +319,7 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st, floa
 
 int run_levels(dis_engine* e, float* host_out = nullptr) {
   const int nl = (int)e->levels.size();
-  CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
+  CU(cudaMemsetAsync(e->counters.p, 0, dis::kCounters * sizeof(unsigned long long), e->stream));
   const int G = std::max(1, std::min(std::min(kMaxGroups, e->max_groups), e->n_pairs));
   while ((int)e->search_ev.size() < 4 * nl * G) {
     cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev);
@@ -355,7 +356,7 @@ int run_levels(dis_engine* e, float* host_out = nullptr) {
 }
 
 int fetch_counters(dis_engine* e) {
-  unsigned long long c[16];
+  unsigned long long c[dis::kCounters];
   CU(cudaMemcpyAsync(c, e->counters.p, sizeof c, cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
 #ifdef DIS_DEBUG_STATS
@@ -364,9 +365,15 @@ int fetch_counters(dis_engine* e) {
           c[4], (double)c[5] / c[4], (double)c[13] / c[4], (double)c[6] / (c[5] ? c[5] : 1), (double)c[7] / c[4], (double)c[8] / (c[7] ? c[7] : 1),
           (double)c[12] / c[4], c[9], c[10], c[11], (double)c[10] / (c[11] ? c[11] : 1));
 #endif
+  if (c[14]) {
+    static char msg[96];
+    snprintf(msg, sizeof msg, "checked build: device assertion %llu failed (csrc/dis_search.cu DIS_CHECK)", c[14]);
+    return fail(DIS_ERR_CUDA, msg);
+  }
   if (c[15]) return fail(DIS_ERR_CUDA, "internal: k_stragglers timed out waiting for the walk's hand-offs; results are incomplete");
   e->stats.patch_iterations = c[0]; e->stats.sampled_iterations = c[1];
   e->stats.resets = c[2]; e->stats.start_oob = c[3];
+  e->stats.sampled_converge = c[16]; e->stats.sampled_walk = c[17];
   e->stats.kernel_launches = e->launches;
   e->stats_fetched = true;
   return DIS_OK;
@@ -648,6 +655,7 @@ void add_stats(dis_stats* acc, const dis_stats& s) {
   acc->patches += s.patches; acc->patch_iterations += s.patch_iterations;
   acc->sampled_iterations += s.sampled_iterations; acc->resets += s.resets;
   acc->start_oob += s.start_oob; acc->kernel_launches += s.kernel_launches;
+  acc->sampled_converge += s.sampled_converge; acc->sampled_walk += s.sampled_walk;
 }
 
 }  // namespace
@@ -1068,7 +1076,7 @@ int dis_tiled_begin(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, in
   e->stride_u8 = w;
   e->launches = 0;
   if (int rc = run_pyramid_u8(e, w)) return rc;
-  CU(cudaMemsetAsync(e->counters.p, 0, 16 * sizeof(unsigned long long), e->stream));
+  CU(cudaMemsetAsync(e->counters.p, 0, dis::kCounters * sizeof(unsigned long long), e->stream));
   for (Level& L : e->levels)   // patches outside this GPU's bands are filled in by dis_tiled_set_u
     CU(cudaMemsetAsync(L.u.p, 0, 2 * sizeof(float) * (size_t)L.info.num_patches, e->stream));
   const int nl = (int)e->levels.size();

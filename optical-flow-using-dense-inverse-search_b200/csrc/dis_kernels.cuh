@@ -33,7 +33,7 @@ struct SearchArgs {
   const float* init_override; // optional explicit per-patch init [pair][np][2] (PatchGrid API); else nullptr
   float* u_out;             // [pair][np][2]
   int* iters_out;           // [pair][np] or nullptr
-  unsigned long long* counters;  // [16]: patch_iterations, sampled_iterations, resets, start_oob, ...; [15] = internal error flag (or nullptr)
+  unsigned long long* counters;  // [kCounters]: patch_iterations, sampled_iterations, resets, start_oob, (4-13: DIS_DEBUG_STATS), [15] = internal error flag, [16]/[17] sampled passes of k_converge / of the walk (or nullptr)
   void* stragglers;         // hand-off list for patches that miss on every pass (or nullptr: no hand-off)
   int* straggler_count;     // [0] entries appended, [1] entries claimed by k_stragglers, [2] "walk finished" flag,
                             // [3] blocks of the walk that have started (device)
@@ -60,6 +60,7 @@ struct SearchArgs {
   int conv_min;             // k_converge: a warp's batch may leave after this many passes once each of its patches has re-sampled a seen position
   float early_step;         // k_converge -> k_stragglers when the last passes still move by this much (px); 0 = never (set by the launcher)
   int tile_margin;          // ceil(outlierthresh) + 1: how far (px) a tap base can move from the start position's before a reset
+  long long walk_capacity;  // patches the hand-off buffers (walk_state / walk_seeds) of this launch can hold (checked builds)
   float one;                // 1.0f, set by the launcher: a run-time constant that keeps ptxas from contracting packed mul + add (dis_search.cu)
 };
 
@@ -93,9 +94,21 @@ int current_device();
 // multiProcessorCount of the current device (cached per device)
 int sm_count();
 
+// Checked build (-DDIS_CHECKED, tools/variants.sh): device-side bounds assertions on every class of address the search
+// kernels form (plane taps, template gathers, hand-off records, straggler list slots, shared-memory tiles).  A violated
+// check records its code in counters[14]; the host turns it into DIS_ERR_CUDA.  compute-sanitizer is closed on the
+// B200 pool this was developed on, so the GPU test-suite run against the checked build is the evidence instead
+// (profiles/r2_checked_build_pytest.log).
+#ifdef DIS_CHECKED
+#define DIS_CHECK(A, cond, code) do { if (!(cond) && (A).counters) atomicMax((A).counters + 14, (unsigned long long)(code)); } while (0)
+#else
+#define DIS_CHECK(A, cond, code) ((void)0)
+#endif
+
 #ifndef DIS_SLOTS
 #define DIS_SLOTS 16
 #endif
+constexpr int kCounters = 24;
 constexpr int kStragglerBytes = 32;      // one entry of the walk -> k_stragglers hand-off list
 constexpr int kWalkSeeds = DIS_SLOTS;   // entries of a patch's {position -> delta_u} cache (16 or 32)
 constexpr size_t kWalkBytesPerPatch = 32 + 16 * kWalkSeeds;   // walk_state + walk_seeds

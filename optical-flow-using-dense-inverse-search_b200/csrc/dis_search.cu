@@ -410,7 +410,22 @@ struct Window8P {
 };
 
 // sample_window8<4> + normalise_and_project<8, 4> on pairs: same operations, same order, half the instructions.
-__device__ __forceinline__ float2 sample_window8p(const Window8P& Wn, float opx, float opy, int patnorm, const Template8P& T, float onef) {
+// The packed template gradients of a ps-8 patch in shared memory: element r of the lane at base[r * 32] (x) and
+// base[(8 + r) * 32] (y); base already points at the lane's column.  Holding them there instead of in 32 registers
+// lets k_converge run 6 warps per scheduler instead of 4 — the kernel is bound by dependent-issue latency, not by
+// the issue rate or the FP32 pipe.
+struct Template8S {
+  const f32x2* base;
+  __device__ __forceinline__ f32x2 x(int r) const { return base[r * 32]; }
+  __device__ __forceinline__ f32x2 y(int r) const { return base[(8 + r) * 32]; }
+};
+struct Template8R {   // register-resident variant with the same interface
+  const Template8P* t;
+  __device__ __forceinline__ f32x2 x(int r) const { return t->x[r]; }
+  __device__ __forceinline__ f32x2 y(int r) const { return t->y[r]; }
+};
+template <typename TA>
+__device__ __forceinline__ float2 sample_window8p(const Window8P& Wn, float opx, float opy, int patnorm, const TA T, float onef) {
   const float fl = floorf(opx), fk = floorf(opy);
   const float a = opx - fl, b = opy - fk;
   const float w0 = (1 - a) * (1 - b), w1 = a * (1 - b), w2 = b * (1 - a), w3 = a * b;
@@ -427,7 +442,7 @@ __device__ __forceinline__ float2 sample_window8p(const Window8P& Wn, float opx,
   }
   f32x2 px[8], py[8];
 #pragma unroll
-  for (int r = 0; r < 8; ++r) { px[r] = mul2(T.x[r], v[r]); py[r] = mul2(T.y[r], v[r]); }
+  for (int r = 0; r < 8; ++r) { px[r] = mul2(T.x(r), v[r]); py[r] = mul2(T.y(r), v[r]); }
   return make_float2(tree_sum_p(px, one), tree_sum_p(py, one));
 }
 
@@ -438,6 +453,13 @@ __device__ __forceinline__ bool must_reset(float px, float py, float stx, float 
   const float ddx = stx - px, ddy = sty - py;
   const float s = ddx * ddx + ddy * ddy;
   return !(s <= A.out2max) || px < A.lb || py < A.lb || px > A.ub_w || py > A.ub_h || px != px || py != py;
+}
+
+// (checked builds) is the ps x ps gather around plane offset c, or the (ps+1) x (ps+1) tap window ending at it, inside the padded plane?
+template <int PS>
+__device__ __forceinline__ bool gather_in_plane(const SearchArgs& A, int c) {
+  const int th = A.height + 2 * A.pad, y = c / A.tmp_w, x = c - y * A.tmp_w;
+  return c >= 0 && x - PS / 2 - 1 >= 0 && x + PS / 2 - 1 < A.tmp_w && y - PS / 2 - 1 >= 0 && y + PS / 2 - 1 < th;
 }
 
 // Insert {position bits -> delta_u} into a patch's 16-slot cache image (slot s at cache[s * STRIDE]).
@@ -531,11 +553,14 @@ __device__ __forceinline__ float2 patch_init(const SearchArgs& A, int idx, int p
 // gradients, LU factors and (ps 8) the tap window stay in registers, a pass is pure fp32 arithmetic.
 // Patches that end here (start out of bounds, reset, max_iter < kN1, conv_eps) are written out;
 // the others leave {u, k, LU} and their last kSeed {position -> delta_u} pairs for the walk phase.
+#ifndef DIS_CONV_TSMEM
+#define DIS_CONV_TSMEM 0     // ps 8: 1 = packed template gradients in shared memory (80 registers, 24 warps per SM): measured SLOWER (9.2 vs 7.5 ms per step), kept as an experiment
+#endif
 #ifndef DIS_CONV_WARPS
 #define DIS_CONV_WARPS 8
 #endif
 #ifndef DIS_CONV_BLOCKS
-#define DIS_CONV_BLOCKS 2
+#define DIS_CONV_BLOCKS (DIS_CONV_TSMEM && DIS_PACKED ? 3 : 2)
 #endif
 // ps <= 8: 8 warps x 2 blocks at <= 128 registers; larger patches keep more elements per lane and get the full register file
 __host__ __device__ constexpr int conv_warps(int ps) { return ps <= 8 ? DIS_CONV_WARPS : 4; }
@@ -556,6 +581,9 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
   WalkState* __restrict__ states = reinterpret_cast<WalkState*>(A.walk_state);
   uint4* __restrict__ seeds = reinterpret_cast<uint4*>(A.walk_seeds);
   __shared__ uint4 images[kConvWarps][G::G * kSlots];         // the walk phase's cache image of each patch
+  constexpr bool kPacked = DIS_PACKED && PS == 8 && SG == 4;
+  constexpr bool kTsmem = kPacked && DIS_CONV_TSMEM;
+  __shared__ f32x2 tsm[kTsmem ? kConvWarps : 1][16][32];      // packed template gradients, [element][lane]
   uint4* img_warp = images[threadIdx.x >> 5];
   uint4* img = img_warp + sub * kSlots;
   unsigned long long c_iters = 0;
@@ -578,6 +606,9 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
         reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
     const float* __restrict__ imB = A.planes.base + (size_t)fr.y * A.planes.frame_stride;
     float2 T[G::NPL];
+    DIS_CHECK(A, idx >= 0 && idx < total && (long long)idx < A.walk_capacity, 101);
+    DIS_CHECK(A, g.pair >= 0 && g.pair < A.n_pairs && g.pid >= 0 && g.pid < A.np, 102);
+    DIS_CHECK(A, gather_in_plane<PS>(A, (g.ry + A.pad) * tw + (g.rx + A.pad) + tw + 1), 103);   // template gather: rows/cols -ps/2 .. ps/2-1
     load_template<PS, SG>(gxyA, (g.ry + A.pad) * tw + (g.rx + A.pad), tw, sl, eoff, T);
     LU2 lu;
     {
@@ -586,11 +617,17 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
       fix_singular(h00, h.y, h11);
       lu.factor(h00, h.y, h11);
     }
-    constexpr bool kPacked = DIS_PACKED && PS == 8 && SG == 4;
     typename std::conditional<kPacked, Window8P, Window8<SG>>::type Wn;
     Wn.bx = -1; Wn.by = -1;
     Template8P Tp;
-    if constexpr (kPacked) Tp.set(T);
+    if constexpr (kPacked && !kTsmem) Tp.set(T);
+    if constexpr (kTsmem) {
+      __syncwarp();
+      f32x2* t = &tsm[threadIdx.x >> 5][0][lane];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) { t[r * 32] = pk2(T[r].x, T[8 + r].x); t[(8 + r) * 32] = pk2(T[r].y, T[8 + r].y); }
+      __syncwarp();
+    }
     int k = 0;
     unsigned ns = 0, fifo = 0;
     float moved = 0.f;                                        // largest |delta u| component of the last three passes
@@ -610,8 +647,10 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
       float2 sg;
       if constexpr (PS == 8) {
         const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
+        DIS_CHECK(A, gather_in_plane<PS>(A, tb.y * tw + tb.x), 104);   // tap window: rows/cols base-ps/2-1 .. base+ps/2-1
         if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) Wn.load(imB, tw, sl, tb.x, tb.y);
-        if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Tp, A.one);
+        if constexpr (kTsmem) sg = sample_window8p(Wn, px, py, A.patnorm, Template8S{&tsm[threadIdx.x >> 5][0][lane]}, A.one);
+        else if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Template8R{&Tp}, A.one);
         else sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
@@ -674,6 +713,7 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
     if (lane == 0 && (c_iters | c_sampled | c_resets | c_oob)) {
       atomicAdd(&A.counters[0], c_iters);
       atomicAdd(&A.counters[1], (unsigned long long)c_sampled);
+      atomicAdd(&A.counters[16], (unsigned long long)c_sampled);   // sampled passes of k_converge
       atomicAdd(&A.counters[2], (unsigned long long)c_resets);
       atomicAdd(&A.counters[3], (unsigned long long)c_oob);
     }
@@ -727,6 +767,7 @@ k_inverse_search(const SearchArgs A) {
 #endif
       if (state == ST_FREE) {
         idx = base + __popc(free_m & ((1u << lane) - 1u));
+        DIS_CHECK(A, idx >= 0 && (idx >= total || (long long)idx < A.walk_capacity), 201);
         if (idx < total) {
           const float4 w0 = reinterpret_cast<const float4*>(A.walk_state)[2 * (size_t)idx];
           k = __float_as_int(w0.z);
@@ -833,6 +874,7 @@ k_inverse_search(const SearchArgs A) {
         else if (k > iters) fin = true;
         else {
           const int slot = atomicAdd(A.straggler_count, 1);
+          DIS_CHECK(A, slot >= 0, 205);
           if (slot < A.straggler_cap) {
             Straggler* rec = reinterpret_cast<Straggler*>(A.stragglers) + slot;
             *reinterpret_cast<float4*>(rec) = make_float4(__int_as_float(pair), __int_as_float(patch_geom(A, idx).pid), ux, uy);
@@ -867,8 +909,11 @@ k_inverse_search(const SearchArgs A) {
 #pragma unroll 1
       for (int base = 0; base < nserv; base += G::G) {
         const int src = W.list[min(base + sub, nserv - 1)];
+        DIS_CHECK(A, src >= 0 && src < 32, 202);
         const float opx = __shfl_sync(kFull, px, src), opy = __shfl_sync(kFull, py, src);
         const int oc = __shfl_sync(kFull, coff, src), opair = __shfl_sync(kFull, pair, src);
+        DIS_CHECK(A, opair >= 0 && opair < A.n_pairs && gather_in_plane<PS>(A, oc + tw + 1), 203);
+        { const int2 tbc = tap_base<PS>(opx, opy, A.pad, wmax, hmax); DIS_CHECK(A, gather_in_plane<PS>(A, tbc.y * tw + tbc.x), 204); }
         const int2 fr = A.pairs[opair];
         const float2* __restrict__ gxyA =
             reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
@@ -920,6 +965,7 @@ k_inverse_search(const SearchArgs A) {
     if (lane == 0 && (c_iters | c_sampled | c_resets | c_oob)) {
       atomicAdd(&A.counters[0], c_iters);
       atomicAdd(&A.counters[1], (unsigned long long)c_sampled);
+      atomicAdd(&A.counters[17], (unsigned long long)c_sampled);   // sampled passes of the walk
       atomicAdd(&A.counters[2], (unsigned long long)c_resets);
       atomicAdd(&A.counters[3], (unsigned long long)c_oob);
     }
@@ -1005,6 +1051,8 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
       const float4 f = __ldcg(reinterpret_cast<const float4*>(rec));
       e.pair = __float_as_int(f.x); e.pid = __float_as_int(f.y); e.ux = f.z; e.uy = f.w; e.k = ld_volatile(&rec->k);
     }
+    DIS_CHECK(A, e.pair >= 0 && e.pair < A.n_pairs && e.pid >= 0 && e.pid < A.np && e.k >= 0 && e.k <= A.iterations + 1, 301);
+    DIS_CHECK(A, base >= 0 && base + nclaim <= A.straggler_cap, 302);
     const int2 fr = A.pairs[e.pair];
     const float2* __restrict__ gxyA =
         reinterpret_cast<const float2*>(A.planes.base + (size_t)fr.x * A.planes.frame_stride + A.planes.plane_stride);
@@ -1045,6 +1093,7 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
       const int2 tb0 = tap_base<PS>(stx, sty, A.pad, wmax, hmax);
       ox = min(max(tb0.x - 5 - kTileMargin, 0), tw - kTile);
       oy = min(max(tb0.y - 5 - kTileMargin, 0), th - kTile);
+      DIS_CHECK(A, ox >= 0 && oy >= 0 && ox + kTile <= tw && oy + kTile <= th, 303);
       __syncwarp();
       for (int i = sl; i < kTile * kTile; i += SG) {
         const int r = i / kTile, c = i - r * kTile;
@@ -1060,10 +1109,12 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
         if (__any_sync(kFull, active && (tb.x != Wn.bx || tb.y != Wn.by))) {
           if (use_tile) {   // a base outside the tile belongs to a position the reset test rejects: clamp, result unused
             const int rx = min(max(tb.x - 5 - ox, 0), kTile - 9), ry = min(max(tb.y - 5 - oy, 0), kTile - 9);
+            // an ACTIVE patch (one the reset test has not rejected) must find its true window inside the tile
+            DIS_CHECK(A, !(active && !must_reset(px, py, stx, sty, A)) || (rx == tb.x - 5 - ox && ry == tb.y - 5 - oy), 304);
             Wn.load_tile(tile + ry * kTileStride + rx, kTileStride, sl, tb.x, tb.y);
           } else Wn.load(imB, tw, sl, tb.x, tb.y);
         }
-        if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Tp, A.one);
+        if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Template8R{&Tp}, A.one);
         else sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
@@ -1105,6 +1156,7 @@ template <int PS, int SG, bool FAST>
 int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const SearchSide* side) {
   SearchArgs a = a_in;
   a.one = 1.0f;
+  if (a.walk_capacity <= 0) a.walk_capacity = 1ll << 60;
   constexpr int WSG = (DIS_WALK_SG8 && PS == 8) ? 8 : SG;   // sub-group size of the walk phase's (rare) service rounds
   const size_t smem = (size_t)kWarps * sizeof(WarpSmem);
   static bool attr_done[64] = {false};                        // per template instantiation and device

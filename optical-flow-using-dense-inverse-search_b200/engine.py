@@ -33,7 +33,7 @@ class DisLevelInfo(C.Structure):
 
 class DisStats(C.Structure):
     _fields_ = [(n, C.c_ulonglong) for n in ("patches", "patch_iterations", "sampled_iterations", "resets",
-                                             "start_oob", "kernel_launches")] + [("reserved", C.c_ulonglong * 2)]
+                                             "start_oob", "kernel_launches", "sampled_converge", "sampled_walk")]
 
 
 class DisError(RuntimeError):
@@ -289,7 +289,7 @@ class Engine:
     def stats(self) -> dict:
         s = DisStats()
         _chk(self.lib.dis_get_stats(self._h, C.byref(s)))
-        return {n: int(getattr(s, n)) for n, _ in DisStats._fields_[:6]}
+        return {n: int(getattr(s, n)) for n, _ in DisStats._fields_}
 
 
 def write_flo(path: str, flow: np.ndarray) -> None:

@@ -28,7 +28,8 @@ def shard_frames(n_frames: int, world: int, rank: int) -> Tuple[int, int]:
     return (lo, hi + 1) if hi > lo else (0, 0)
 
 
-STAT_KEYS = ("patches", "patch_iterations", "sampled_iterations", "resets", "start_oob", "kernel_launches")
+STAT_KEYS = ("patches", "patch_iterations", "sampled_iterations", "resets", "start_oob", "kernel_launches",
+             "sampled_converge", "sampled_walk")
 
 
 def reduce_stats(stats: Dict[str, int], device_ms: float, dist=None, device=None) -> Dict[str, float]:

@@ -59,3 +59,26 @@ def test_cli_sequence_outputs(cli, tmp_path, oracle_port):
         assert raw.startswith(b"P6\n128 64\n255\n")
         rgb = np.frombuffer(raw[-3 * 128 * 64:], np.uint8).reshape(64, 128, 3)
         assert np.array_equal(rgb[..., ::-1], oracle_port.color_code(ref[i]))
+
+
+@pytest.mark.gpu
+def test_cli_sequence_longer_than_one_chunk(cli, tmp_path, oracle_port):
+    """131 frames = 130 pairs: the engine works in chunks of 128 pairs; every output must still belong to its own pair."""
+    frames, _ = dis_b200.synth.make_sequence(131, 64, 48, seed=12)
+    os.makedirs(tmp_path / "long")
+    for i, fr in enumerate(frames):
+        write_pgm(tmp_path / "long" / f"frame_{i + 1:04d}.pgm", fr)
+    r = subprocess.run([cli, "long", "1", "131", "30", "8", "2", "0", "0.7", "1", "0"], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout.count("finish long/frame_") == 130
+    e = dis_b200.Engine(0, max_iter=30, coarsest_scale=2)
+    try:
+        for i in (0, 1, 127, 128, 129):
+            ref = e.run_pair(frames[i], frames[i + 1])
+            flo = dis_b200.read_flo(str(tmp_path / "OF_long" / f"frame_{i + 1:04d}.flo"))
+            assert np.array_equal(flo.view(np.uint32), ref.view(np.uint32)), f"pair {i}"
+            raw = open(tmp_path / "OF_long" / f"frame_{i + 1:04d}.ppm", "rb").read()
+            rgb = np.frombuffer(raw[-3 * 64 * 48:], np.uint8).reshape(48, 64, 3)
+            assert np.array_equal(rgb[..., ::-1], oracle_port.color_code(ref)), f"colour image of pair {i}"
+    finally:
+        e.close()

@@ -38,7 +38,7 @@ def _worker(rank, world, port, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     lo, hi = shard_pairs(49, world, rank)
     st = {"patches": (hi - lo) * 149632, "patch_iterations": (hi - lo) * 1000, "sampled_iterations": hi - lo,
-          "resets": rank, "start_oob": 0, "kernel_launches": 25}
+          "resets": rank, "start_oob": 0, "kernel_launches": 25, "sampled_converge": 0, "sampled_walk": 0}
     red = reduce_stats(st, 10.0 + rank, dist)
     got = gather_results(list(range(lo, hi)), dist)
     dist.barrier()

@@ -103,7 +103,8 @@ int main(int argc, char** argv) {
     std::printf("start %s\n", frame_name(folder, start_num_img + i, "pgm").c_str());
     const float* flow = flows.data() + (size_t)2 * w * h * i;
     if (dis_write_flo(frame_name(out_folder, start_num_img + i, "flo").c_str(), flow, w, h) != DIS_OK ||
-        dis_color_code_pair(e, i, -1.f, bgr.data()) != DIS_OK) {   // draw_optical_flow(flowout, dst2), main.cpp:200-201
+        dis_color_code(e, flow, w, h, -1.f, bgr.data()) != DIS_OK) {   // draw_optical_flow(flowout, dst2), main.cpp:200-201
+      // (from the host flow: the engine keeps only the last chunk of <= 128 pairs of a long sequence on the device)
       std::fprintf(stderr, "%s\n", dis_last_error());
       dis_destroy(e);
       return 1;
