@@ -158,6 +158,31 @@ def workload_config(max_iter: int = 1000) -> dict:
             "l2": "per-step working set ~0.6 GB (pyramids + flows) exceeds the 126 MB L2; no explicit flush"}
 
 
+def bind_to_gpu_numa(local_rank: int) -> dict:
+    """Pin this process to the CPUs of its GPU's NUMA node BEFORE it allocates pinned host memory, so that the staging
+    buffers of every rank sit behind their own GPU's root port (without this all ranks of a torchrun job inherit the
+    launcher's affinity and their 8 x 175 MB/step of D2H contend on one node)."""
+    import torch
+    info = {"node": None, "cpus": 0}
+    try:
+        pr = torch.cuda.get_device_properties(local_rank)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        info["node"] = node
+        if node >= 0:
+            cpus = set()
+            for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+            allowed = os.sched_getaffinity(0)
+            use = (cpus & allowed) or cpus
+            os.sched_setaffinity(0, use)
+            info["cpus"] = len(use)
+    except Exception as ex:  # noqa: BLE001
+        info["note"] = str(ex)[:120]
+    return info
+
+
 def code_sha():
     """sha256 over the kernel sources: a profile-derived constant (roofline.traffic) is only valid for the code it was
     captured from."""
@@ -202,6 +227,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fast-mode", action="store_true")
     ap.add_argument("--max-iter", type=int, default=1000)
+    ap.add_argument("--no-numa-bind", action="store_true")
+    ap.add_argument("--no-config3", action="store_true")
     ap.add_argument("--ref-strip", type=int, default=0, help="reference arm: crop pairs to their top H rows (0 = whole pairs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -232,6 +259,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    numa = bind_to_gpu_numa(local_rank) if not args.no_numa_bind else {"node": None, "cpus": 0, "note": "--no-numa-bind"}
     frames, gt = bench_sequence(100 + rank)
     eng = dis_b200.Engine(local_rank, max_iter=args.max_iter)
     first = np.arange(N_PAIRS, dtype=np.int32)
@@ -269,22 +297,63 @@ def main():
     for _ in range(args.steps):
         eng.run_sequence_ptr(pin_in.data_ptr(), N_FRAMES, W, H, pin_out.data_ptr())
     e2e_s = time.perf_counter() - t0
+    e2e_local_s = e2e_s
     barrier()
     e2e_s = max_over_ranks(e2e_s)
     clocks = sampler.stop() if sampler else None
     checksum = float(np.abs(pin_out.numpy()).mean())
+    # host <-> device copy rates of this rank's pinned buffers (informational: where the e2e time goes at N GPUs)
+    dev_in = torch.empty_like(pin_in, device="cuda")
+    dev_out = torch.empty_like(pin_out, device="cuda")
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    dev_in.copy_(pin_in, non_blocking=True); dev_out.copy_(pin_out, non_blocking=True); torch.cuda.synchronize()
+    barrier()
+    evs[0].record(); dev_in.copy_(pin_in, non_blocking=True); evs[1].record(); pin_out.copy_(dev_out, non_blocking=True); evs[2].record()
+    torch.cuda.synchronize()
+    copy_rates = {"rank": rank, "numa": numa, "h2d_gbs": pin_in.numel() / (evs[0].elapsed_time(evs[1]) * 1e6),
+                  "d2h_gbs": pin_out.numel() * 4 / (evs[1].elapsed_time(evs[2]) * 1e6), "e2e_ms_per_step": 1e3 * e2e_local_s / args.steps}
+    del dev_in, dev_out
+    eng.run_sequence_ptr(pin_in.data_ptr(), N_FRAMES, W, H, pin_out.data_ptr())   # restore the flows for the parity check
+    if dist is not None:
+        all_rates = [None] * world
+        dist.all_gather_object(all_rates, copy_rates)
+    else:
+        all_rates = [copy_rates]
+
     # parity of what was just timed: the e2e buffer AND the device-resident result against the reference-generated goldens
     parity = None
     if rank == 0 and args.max_iter == 1000:
         parity = parity_check(pin_out.numpy())
+        eng.upload_frames(frames, first, first + 1); eng.run_resident()
         res = parity_check(eng.download_flows())
         parity["resident_run_bit_identical"] = res["bit_identical"]
+
+    # ---- BASELINE config 3 as written: a stream of 4096 independent 1024x436 pairs sharded over the N GPUs (STRONG
+    #      scaling: total work fixed).  64 distinct synthetic pairs, cycled; every pass recomputes everything. ----------
+    config3 = None
+    if not args.no_config3:
+        C3_TOTAL, C3_CHUNK = 4096, 64
+        lo, hi = dis_b200.parallel.shard_pairs(C3_TOTAL // C3_CHUNK, world, rank)     # chunks of 64 pairs, contiguous per rank
+        prs = [dis_b200.synth.make_pair(W, H, seed=300 + i)[:2] for i in range(C3_CHUNK)]
+        fr = np.concatenate([np.stack([p[0] for p in prs]), np.stack([p[1] for p in prs])])
+        idx = np.arange(C3_CHUNK, dtype=np.int32)
+        eng.upload_frames(fr, idx, idx + C3_CHUNK)
+        eng.run_resident(); eng.synchronize()
+        barrier()
+        eng.timer_start()
+        for _ in range(hi - lo):
+            eng.run_resident()
+        c3_ms = max_over_ranks(eng.timer_stop_ms())
+        barrier()
+        config3 = {"workload": "4096 independent synthetic 1024x436 pairs (64 distinct seeds, cycled) sharded over the GPUs in contiguous blocks",
+                   "scaling": "strong", "pairs_total": C3_TOTAL, "n_gpus": world, "seconds": c3_ms * 1e-3,
+                   "value": C3_TOTAL / (c3_ms * 1e-3), "unit": UNIT, "timing": "device (CUDA events), max over ranks, inputs resident"}
 
     # ---- informational: the optional convergence early-out (conv_eps > 0), a REPORTED DEVIATION from the
     #      reference (which has no convergence test); never the headline ------------------------
     fast = None
     if rank == 0 and world == 1 and not args.no_fast_mode:
-        exact = eng.download_flows()
+        exact = pin_out.numpy()           # the exact flows of this sequence (e2e buffer, checked against the goldens above)
         fe = dis_b200.Engine(local_rank, max_iter=args.max_iter, conv_eps=1e-4)
         fe.upload_frames(frames, first, first + 1)
         for _ in range(3):
@@ -374,6 +443,7 @@ def main():
                  "ms_per_level_fine_to_coarse": phase_ms[1]},
                 {"kernel": "k_stragglers<8,4>", "ms_per_step_not_hidden_by_the_walk": strag_ms, "sampled_passes": s_strag,
                  "ms_per_level_fine_to_coarse": phase_ms[2]}],
+            "config3_4096_pairs": config3, "per_rank_copy_rates": all_rates,
             "stats_per_step": st, "stats_job_per_step": job, "search_share_of_step": search_ms / step_ms,
             "clocks": clocks, "checksum": checksum,
         }

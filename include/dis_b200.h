@@ -211,6 +211,50 @@ DIS_API int dis_tiled_get_u(dis_engine* e, int level, void* device_dst);
 DIS_API int dis_tiled_set_u(dis_engine* e, int level, const void* device_src);
 DIS_API int dis_tiled_densify(dis_engine* e, int level);
 DIS_API int dis_tiled_finish(dis_engine* e, float* flow_out);
+/* The same run with a HALO exchange instead of the all-gather, for engines of ONE process (dis_pool_run_pair_tiled_u8
+ * drives these; all calls are asynchronous, cross-GPU ordering is by CUDA events, nothing synchronises between levels):
+ * fetch_u_rows copies grid rows [row0, row1) of `src`'s per-patch flows of the level into e's (src on the same or on a
+ * peer GPU with peer access enabled: the copying SMs read over NVLink) once src has searched them; densify_rows
+ * densifies pixel rows [y0, y1) of the level only (src/patch_grid.cpp:121-182 for those rows — the caller makes sure
+ * the covering patches, ceil(ps / (2 steps)) + 1 grid rows beyond the band, are present); finish_rows crops and
+ * downloads rows [y0, y1) of the result straight into their place in flow_out; dis_tiled_end waits and closes the run. */
+DIS_API int dis_tiled_fetch_u_rows(dis_engine* e, int level, dis_engine* src, int row0, int row1);
+DIS_API int dis_tiled_densify_rows(dis_engine* e, int level, int y0, int y1);
+DIS_API int dis_tiled_finish_rows(dis_engine* e, float* flow_out, int y0, int y1);
+DIS_API int dis_tiled_end(dis_engine* e);
+
+/* ---- several GPUs of one box behind one handle ------------------------------------------------------------------
+ * The reference's unit of independent work is one iteration of its per-pair loop (src/main.cpp:102; the body shares no
+ * state).  A pool holds one engine and one host thread per listed CUDA device; a batch / sequence is cut into
+ * CONTIGUOUS blocks of pairs, one per device (sizes differ by at most one, earlier devices get the longer blocks;
+ * neighbouring blocks of a sequence share one frame so that every device builds each pyramid once), and every block runs
+ * through dis_run_batch_u8 / dis_run_sequence_u8 on its device concurrently.  No collective and no peer traffic: each
+ * GPU writes its flows straight into the caller's buffer.  Results are bit-identical to one engine.  A device may be
+ * listed more than once (two engines on one GPU).  Worker threads bind to the CPUs of their GPU's NUMA node
+ * (DIS_POOL_NO_AFFINITY=1 disables); dis_pool_host_alloc allocates pinned host memory from such a thread. */
+typedef struct dis_pool dis_pool;
+DIS_API int dis_pool_create(const dis_params* p, const int* devices, int n_devices, dis_pool** out);  /* devices NULL: 0..n-1 */
+DIS_API void dis_pool_destroy(dis_pool* pool);
+DIS_API int dis_pool_size(const dis_pool* pool);
+DIS_API int dis_pool_device(const dis_pool* pool, int worker, int* device, int* numa_cpus);  /* numa_cpus: CPUs the thread is bound to (0: not bound) */
+DIS_API const char* dis_pool_last_error(void);
+/* block [lo, hi) of part `part` of `parts`: the sharding rule itself (pure; also used by the host-side tests) */
+DIS_API void dis_pool_shard(int n_pairs, int parts, int part, int* lo, int* hi);
+DIS_API int dis_pool_run_batch_u8(dis_pool* pool, const uint8_t* const* a, const uint8_t* const* b, int n_pairs, int w,
+                                  int h, int stride, float* flow_out);                       /* BASELINE config 3 */
+DIS_API int dis_pool_run_sequence_u8(dis_pool* pool, const uint8_t* frames, int n_frames, int w, int h, int stride,
+                                     size_t frame_stride, float* flow_out);                  /* BASELINE config 2 over N GPUs */
+/* ONE large pair split over the pool's GPUs by bands of grid rows with a per-level halo exchange over NVLink peer
+ * memory (BASELINE config 5).  Every GPU gets both frames and builds the pyramids redundantly (< 1 % of
+ * the work); per level it searches only the patches of its band, pulls the ceil(ps / (2 steps)) + 1 boundary grid rows
+ * it needs from its neighbours, densifies only the pixel rows its next-finer band is initialised from (finest level:
+ * its band of the output) and downloads only that band.  Bit-identical to dis_run_pair_u8.  finest_scale must be 0. */
+DIS_API int dis_pool_run_pair_tiled_u8(dis_pool* pool, const uint8_t* a, const uint8_t* b, int w, int h, int stride,
+                                       float* flow_out);
+DIS_API int dis_pool_get_stats(dis_pool* pool, dis_stats* sum);                              /* summed over the devices of the last call */
+DIS_API int dis_pool_last_ms(dis_pool* pool, double* wall_ms, double* per_worker_ms);        /* host wall clock of the last call */
+DIS_API int dis_pool_host_alloc(dis_pool* pool, int worker, size_t bytes, void** out);       /* pinned, NUMA-local to that worker's GPU */
+DIS_API int dis_pool_host_free(dis_pool* pool, void* ptr);
 
 /* Middlebury colour coding, draw_optical_flow(flow, dst, maxmotion) of src/color_coding.cpp:83-117
  * (called at src/main.cpp:200-201 with maxmotion = -1: the range is the field's own maximum).

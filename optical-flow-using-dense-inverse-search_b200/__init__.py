@@ -8,4 +8,4 @@ The directory name is fixed by the project layout and is not a valid Python iden
   synth.py         seeded synthetic frame pairs / sequences with known flow (inputs only)
 """
 from . import engine, parallel, synth  # noqa: F401
-from .engine import Engine, DisError, default_params, load_library, read_flo, write_flo  # noqa: F401
+from .engine import Engine, Pool, DisError, default_params, load_library, read_flo, write_flo  # noqa: F401

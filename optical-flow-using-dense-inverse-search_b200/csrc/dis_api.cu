@@ -80,6 +80,9 @@ struct dis_engine {
   int n_frames = 0, n_pairs = 0, stride_u8 = 0;
   bool have_run = false;
   bool tiled = false;                   // between dis_tiled_begin and dis_tiled_finish
+  std::vector<cudaEvent_t> tiled_ev;    // per level: "this engine's band of the level has been searched" (row-banded runs)
+  int2 tiled_pr = {0, 1};               // the pair record of a tiled run (outlives the asynchronous upload)
+  unsigned long long tiled_patches = 0; // patches this engine searched in the current tiled run
   bool stats_fetched = false;
   bool out_sent = false;                // the last run already copied its flows to the caller's buffer
   bool keep_iters = true;
@@ -242,7 +245,7 @@ dis::SearchArgs level_search_args(dis_engine* e, int g, int s, int p0, int p1) {
 }
 
 // PatchGrid::densification_and_create_dance_flow for level s, pairs [p0, p1)
-void level_densify(dis_engine* e, int s, int p0, int p1, cudaStream_t st) {
+void level_densify(dis_engine* e, int s, int p0, int p1, cudaStream_t st, int y0 = 0, int y1 = 0) {
   Level& L = e->levels[s];
   const dis_level_info& I = L.info;
   dis::DensifyArgs d;
@@ -250,6 +253,7 @@ void level_densify(dis_engine* e, int s, int p0, int p1, cudaStream_t st) {
   d.dense = L.flow.as<float>() + L.flow_stride * p0; d.dense_stride = L.flow_stride;
   d.n_pairs = p1 - p0; d.width = I.width; d.height = I.height; d.npw = I.npw; d.nph = I.nph;
   d.offw = I.offw; d.offh = I.offh; d.steps = I.steps; d.np = I.num_patches; d.ps = e->prm.patch_size;
+  d.y0 = y0; d.y1 = y1;
   e->launches += dis::launch_densify(d, st);
 }
 
@@ -723,8 +727,8 @@ int dis_run_pyramids(dis_engine* e, const float* const* img_first, const float* 
   CU(cudaSetDevice(e->device));
   e->w0 = width; e->h0 = height; e->left = 0; e->top = 0;
   if (int rc = setup_run(e, width, height, img_padding, 2, 1)) return rc;
-  const int2 pr = make_int2(0, 1);
-  CU(cudaMemcpyAsync(e->pairs.p, &pr, sizeof pr, cudaMemcpyHostToDevice, e->stream));
+  e->tiled_pr = make_int2(0, 1);
+  CU(cudaMemcpyAsync(e->pairs.p, &e->tiled_pr, sizeof e->tiled_pr, cudaMemcpyHostToDevice, e->stream));
   for (const Level& L : e->levels) {
     const int s = L.info.scale;
     if (!img_first_dx[s] || !img_first_dy[s] || !img_second[s]) return fail(DIS_ERR_PARAM, "null pyramid plane");
@@ -1071,8 +1075,8 @@ int dis_tiled_begin(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, in
   if (e->frames_u8.ensure(fbytes * 2)) return fail(DIS_ERR_ALLOC, "cudaMalloc(frames) failed");
   CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>(), w, a, stride, w, h, cudaMemcpyHostToDevice, e->stream));
   CU(cudaMemcpy2DAsync(e->frames_u8.as<uint8_t>() + fbytes, w, b, stride, w, h, cudaMemcpyHostToDevice, e->stream));
-  const int2 pr = make_int2(0, 1);
-  CU(cudaMemcpyAsync(e->pairs.p, &pr, sizeof pr, cudaMemcpyHostToDevice, e->stream));
+  e->tiled_pr = make_int2(0, 1);
+  CU(cudaMemcpyAsync(e->pairs.p, &e->tiled_pr, sizeof e->tiled_pr, cudaMemcpyHostToDevice, e->stream));
   e->stride_u8 = w;
   e->launches = 0;
   if (int rc = run_pyramid_u8(e, w)) return rc;
@@ -1081,8 +1085,9 @@ int dis_tiled_begin(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, in
     CU(cudaMemsetAsync(L.u.p, 0, 2 * sizeof(float) * (size_t)L.info.num_patches, e->stream));
   const int nl = (int)e->levels.size();
   while ((int)e->search_ev.size() < 4 * nl) { cudaEvent_t ev; CU(cudaEventCreate(&ev)); e->search_ev.push_back(ev); }
+  while ((int)e->tiled_ev.size() < nl) { cudaEvent_t ev; CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); e->tiled_ev.push_back(ev); }
   e->n_groups = 1; e->search_launches = nl;
-  CU(cudaStreamSynchronize(e->stream));   // `pr` is on the stack
+  e->tiled_patches = 0;
   e->have_run = false; e->tiled = true;
   return DIS_OK;
 }
@@ -1094,16 +1099,81 @@ int dis_tiled_search(dis_engine* e, int level, int row0, int row1) {
   if (level < 0 || level >= nl) return fail(DIS_ERR_PARAM, "level out of range");
   const dis_level_info& I = e->levels[level].info;
   if (row0 < 0 || row1 > I.nph || row0 > row1) return fail(DIS_ERR_PARAM, "grid rows out of range");
-  if (row0 == row1) return DIS_OK;   // an empty band (more GPUs than grid rows)
   CU(cudaSetDevice(e->device));
+  if (row0 == row1) {                // an empty band (more GPUs than grid rows)
+    CU(cudaEventRecord(e->tiled_ev[level], e->stream));
+    return DIS_OK;
+  }
   dis::SearchArgs a = level_search_args(e, 0, level, 0, 1);
   a.band_y0 = row0; a.band_h = row1 - row0;
+  e->tiled_patches += (unsigned long long)I.npw * (row1 - row0);
   cudaEvent_t* ev = &e->search_ev[4 * (nl - 1 - level)];
   const int n = dis::launch_inverse_search(a, e->prm.patch_size, e->stream, ev, e->side.stream ? &e->side : nullptr);
   if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
   e->launches += n;
   CU(cudaGetLastError());
+  CU(cudaEventRecord(e->tiled_ev[level], e->stream));
   return DIS_OK;
+}
+
+// ---- halo exchange of a row-banded run, device to device (src/patch_grid.cpp:108-119, 121-182 define
+//      what a band needs: the covering patches of the pixel rows it densifies, and the coarser-flow rows its patches
+//      are initialised from).  All calls are asynchronous: e's stream waits for src's search of the level by event.
+int dis_tiled_fetch_u_rows(dis_engine* e, int level, dis_engine* src, int row0, int row1) {
+  if (!e || !src) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->tiled || !src->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first (both engines)");
+  const int nl = (int)e->levels.size();
+  if (level < 0 || level >= nl || (int)src->levels.size() != nl) return fail(DIS_ERR_PARAM, "level out of range");
+  const dis_level_info& I = e->levels[level].info;
+  if (src->levels[level].info.num_patches != I.num_patches) return fail(DIS_ERR_PARAM, "engines run different geometries");
+  if (row0 < 0 || row1 > I.nph || row0 > row1) return fail(DIS_ERR_PARAM, "grid rows out of range");
+  if (row0 == row1 || e == src) return DIS_OK;
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamWaitEvent(e->stream, src->tiled_ev[level], 0));
+  e->launches += dis::launch_copy_u_rows(src->levels[level].u.as<float>(), e->levels[level].u.as<float>(), I.npw, I.nph,
+                                         row0, row1 - row0, e->stream);
+  CU(cudaGetLastError());
+  return DIS_OK;
+}
+
+int dis_tiled_densify_rows(dis_engine* e, int level, int y0, int y1) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  if (level < 0 || level >= (int)e->levels.size()) return fail(DIS_ERR_PARAM, "level out of range");
+  const dis_level_info& I = e->levels[level].info;
+  if (y0 < 0 || y1 > I.height || y0 > y1) return fail(DIS_ERR_PARAM, "pixel rows out of range");
+  if (y0 == y1) return DIS_OK;
+  CU(cudaSetDevice(e->device));
+  level_densify(e, level, 0, 1, e->stream, y0, y1);
+  CU(cudaGetLastError());
+  return DIS_OK;
+}
+
+// crop + download of output rows [y0, y1) only (rows of the un-padded frame); asynchronous — dis_tiled_end waits
+int dis_tiled_finish_rows(dis_engine* e, float* flow_out, int y0, int y1) {
+  if (!e || !flow_out) return fail(DIS_ERR_PARAM, "null argument");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  if (e->prm.finest_scale != 0) return fail(DIS_ERR_PARAM, "row-banded download needs finest_scale == 0");
+  if (y0 < 0 || y1 > e->h0 || y0 > y1) return fail(DIS_ERR_PARAM, "output rows out of range");
+  if (y0 == y1) return DIS_OK;
+  CU(cudaSetDevice(e->device));
+  Level& L = e->levels[0];
+  const size_t row = 2 * (size_t)e->w0;
+  if (e->out.ensure(sizeof(float) * row * e->h0)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
+  e->launches += dis::launch_crop(L.flow.as<float>(), L.flow_stride, L.info.width, L.info.height, e->left, e->top + y0,
+                                  e->out.as<float>() + row * y0, e->w0, y1 - y0, 1, e->stream);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(flow_out + row * y0, e->out.as<float>() + row * y0, sizeof(float) * row * (y1 - y0), cudaMemcpyDeviceToHost, e->stream));
+  return DIS_OK;
+}
+
+int dis_tiled_end(dis_engine* e) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
+  CU(cudaSetDevice(e->device));
+  e->stats.patches = e->tiled_patches;   // this engine's bands; the counters below are its share too
+  e->have_run = true; e->stats_fetched = false; e->tiled = false;
+  return fetch_counters(e);           // synchronises the stream
 }
 
 static int tiled_copy_u(dis_engine* e, int level, void* dst, const void* src, bool get) {

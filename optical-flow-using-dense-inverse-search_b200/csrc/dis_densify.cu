@@ -17,9 +17,9 @@ __device__ __forceinline__ int floor_div(int a, int b) { return a >= 0 ? a / b :
 
 __global__ void __launch_bounds__(256) k_densify(const DensifyArgs A) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  const int y = A.y0 + blockIdx.y * blockDim.y + threadIdx.y;
   const int pair = blockIdx.z;
-  if (x >= A.width || y >= A.height) return;
+  if (x >= A.width || y >= A.y1) return;
   const int half = A.ps / 2;
   // patch (gx,gy) with centre c covers pixels c-half .. c+half-1  <=>  x-half+1 <= c <= x+half
   int gx_lo = ceil_div_pos(x - half + 1 - A.offw, A.steps), gx_hi = floor_div(x + half - A.offw, A.steps);
@@ -39,6 +39,16 @@ __global__ void __launch_bounds__(256) k_densify(const DensifyArgs A) {
   reinterpret_cast<float2*>(A.dense + (size_t)pair * A.dense_stride)[(size_t)y * A.width + x] = make_float2(sx, sy);
 }
 
+// Halo exchange of a row-banded run: grid rows [row0, row0 + nrows) of the per-patch flows.  `src` may
+// live on a PEER GPU (peer access enabled): the loads then travel over NVLink, issued by this GPU's SMs.
+__global__ void __launch_bounds__(256) k_copy_u_rows(const float2* __restrict__ src, float2* __restrict__ dst, int npw,
+                                                     int nph, int row0, int nrows) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npw * nrows) return;
+  const int gx = i / nrows, gy = row0 + (i - gx * nrows);
+  dst[(size_t)gx * nph + gy] = src[(size_t)gx * nph + gy];
+}
+
 __global__ void __launch_bounds__(256) k_crop(const float2* __restrict__ dense, size_t dense_stride2, int W,
                                               int left, int top, float2* __restrict__ out, int w, int h) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -48,10 +58,12 @@ __global__ void __launch_bounds__(256) k_crop(const float2* __restrict__ dense, 
   out[((size_t)pair * h + y) * w + x] = dense[(size_t)pair * dense_stride2 + (size_t)(y + top) * W + (x + left)];
 }
 
-// src/main.cpp:192-198: flowout *= sc; cv::resize(sc, sc, INTER_LINEAR); crop.  OpenCV's
-// INTER_LINEAR maps destination pixel d to source (d + 0.5)/sc - 0.5, clamps the tap indices to
-// the image and lerps; the arithmetic below is fp32 in that form (this epilogue is exercised by no
-// BASELINE config and is not parity-gated bit for bit — OpenCV 2.4's resize is not available here).
+// src/main.cpp:192-198: flowout *= sc; cv::resize(sc, sc, INTER_LINEAR); crop.  OpenCV's INTER_LINEAR for fp32 is
+// separable and runs in fp32 without FMA: destination x -> source fx = (x + 0.5) / sc - 0.5, sx = floor(fx), weights
+// (1 - (fx - sx), fx - sx); HORIZONTALLY a tap index outside the row is clamped and its weight set to 0 (resize.cpp,
+// xofs/alpha set-up), VERTICALLY only the row indices are clamped and the weights stay (so a border row is
+// S * b0 + S * b1, not S); rows are interpolated horizontally first, then S0 * b0 + S1 * b1.  Restated in exactly that
+// order; bit-identical to cv2.resize (4.13, setUseOptimized(False)) for scales 2, 4, 8 (tests/test_gpu_api.py).
 __global__ void __launch_bounds__(256) k_upsample_crop(const float2* __restrict__ dense, size_t dense_stride2,
                                                        int Wf, int Hf, int finest, int left, int top,
                                                        float2* __restrict__ out, int w, int h) {
@@ -61,26 +73,39 @@ __global__ void __launch_bounds__(256) k_upsample_crop(const float2* __restrict_
   if (x >= w || y >= h) return;
   const float sc = (float)(1 << finest), inv = 1.0f / sc;
   const float fx = ((float)(x + left) + 0.5f) * inv - 0.5f, fy = ((float)(y + top) + 0.5f) * inv - 0.5f;
-  int x0 = (int)floorf(fx), y0 = (int)floorf(fy);
-  float ax = fx - (float)x0, ay = fy - (float)y0;
+  int x0 = (int)floorf(fx), sy = (int)floorf(fy);
+  float ax = fx - (float)x0;
+  const float ay = fy - (float)sy;
   if (x0 < 0) { x0 = 0; ax = 0.f; }
-  if (y0 < 0) { y0 = 0; ay = 0.f; }
-  int x1 = x0 + 1, y1 = y0 + 1;
-  if (x0 >= Wf - 1) { x0 = Wf - 1; x1 = Wf - 1; ax = 0.f; }
-  if (y0 >= Hf - 1) { y0 = Hf - 1; y1 = Hf - 1; ay = 0.f; }
+  if (x0 >= Wf - 1) { x0 = Wf - 1; ax = 0.f; }
+  const int x1 = min(x0 + 1, Wf - 1);
+  const int y0 = min(max(sy, 0), Hf - 1), y1 = min(max(sy + 1, 0), Hf - 1);
+  const float a0 = 1.f - ax, a1 = ax, b0 = 1.f - ay, b1 = ay;
   const float2* d = dense + (size_t)pair * dense_stride2;
-  const float2 a = d[(size_t)y0 * Wf + x0], b = d[(size_t)y0 * Wf + x1];
-  const float2 c = d[(size_t)y1 * Wf + x0], e = d[(size_t)y1 * Wf + x1];
-  const float tx0 = a.x * sc + (b.x * sc - a.x * sc) * ax, tx1 = c.x * sc + (e.x * sc - c.x * sc) * ax;
-  const float ty0 = a.y * sc + (b.y * sc - a.y * sc) * ax, ty1 = c.y * sc + (e.y * sc - c.y * sc) * ax;
-  out[((size_t)pair * h + y) * w + x] = make_float2(tx0 + (tx1 - tx0) * ay, ty0 + (ty1 - ty0) * ay);
+  const float2 p00 = d[(size_t)y0 * Wf + x0], p01 = d[(size_t)y0 * Wf + x1];
+  const float2 p10 = d[(size_t)y1 * Wf + x0], p11 = d[(size_t)y1 * Wf + x1];
+  const float hx0 = (p00.x * sc) * a0 + (p01.x * sc) * a1, hx1 = (p10.x * sc) * a0 + (p11.x * sc) * a1;
+  const float hy0 = (p00.y * sc) * a0 + (p01.y * sc) * a1, hy1 = (p10.y * sc) * a0 + (p11.y * sc) * a1;
+  out[((size_t)pair * h + y) * w + x] = make_float2(hx0 * b0 + hx1 * b1, hy0 * b0 + hy1 * b1);
 }
 
 }  // namespace
 
-int launch_densify(const DensifyArgs& a, cudaStream_t s) {
-  dim3 b(32, 8), g((a.width + 31) / 32, (a.height + 7) / 8, a.n_pairs);
+int launch_densify(const DensifyArgs& a_in, cudaStream_t s) {
+  DensifyArgs a = a_in;
+  if (a.y1 <= a.y0) { a.y0 = 0; a.y1 = a.height; }
+  a.y0 = a.y0 < 0 ? 0 : a.y0;
+  a.y1 = a.y1 > a.height ? a.height : a.y1;
+  if (a.y1 <= a.y0) return 0;
+  dim3 b(32, 8), g((a.width + 31) / 32, (a.y1 - a.y0 + 7) / 8, a.n_pairs);
   k_densify<<<g, b, 0, s>>>(a);
+  return 1;
+}
+
+int launch_copy_u_rows(const float* src, float* dst, int npw, int nph, int row0, int nrows, cudaStream_t s) {
+  if (nrows <= 0) return 0;
+  const int n = npw * nrows;
+  k_copy_u_rows<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float2*>(src), reinterpret_cast<float2*>(dst), npw, nph, row0, nrows);
   return 1;
 }
 

@@ -69,6 +69,7 @@ struct DensifyArgs {
   float* dense;             // [pair][h][w][2]
   size_t dense_stride;      // floats per pair
   int n_pairs, width, height, npw, nph, offw, offh, steps, np, ps;
+  int y0, y1;               // pixel rows [y0, y1) to densify (y1 <= y0: all rows) — row-banded runs over several GPUs
 };
 
 // Development knobs, read from the environment ONCE per process (first use) and never in launch code.  The defaults
@@ -120,6 +121,9 @@ struct SearchSide { cudaStream_t stream; cudaEvent_t fork, join; unsigned blocks
 int launch_inverse_search(const SearchArgs& a, int patch_size, cudaStream_t s, cudaEvent_t* ev = nullptr,
                           const SearchSide* side = nullptr);
 int launch_densify(const DensifyArgs& a, cudaStream_t s);
+// grid rows [row0, row0 + nrows) of a level's per-patch flows (x-major: u[gx * nph + gy]) from src (this or a peer
+// device, read over NVLink by the copying SMs) into dst
+int launch_copy_u_rows(const float* src, float* dst, int npw, int nph, int row0, int nrows, cudaStream_t s);
 
 struct PyramidArgs {
   const uint8_t* frames;    // [frame][h0][stride0] u8 (un-padded input frames), or nullptr if f32 input

@@ -53,6 +53,10 @@ ABI_SYMBOLS = [
     "dis_grid_num_patches", "dis_grid_get_patch", "dis_write_flo", "dis_read_flo", "dis_read_flo_size",
     "dis_color_code", "dis_color_code_pair", "dis_tiled_begin", "dis_tiled_search", "dis_tiled_get_u", "dis_tiled_set_u",
     "dis_tiled_densify", "dis_tiled_finish",
+    "dis_pool_create", "dis_pool_destroy", "dis_pool_size", "dis_pool_device", "dis_pool_last_error", "dis_pool_shard",
+    "dis_pool_run_batch_u8", "dis_pool_run_sequence_u8", "dis_pool_get_stats", "dis_pool_last_ms", "dis_pool_host_alloc",
+    "dis_pool_host_free", "dis_pool_run_pair_tiled_u8", "dis_tiled_fetch_u_rows", "dis_tiled_densify_rows",
+    "dis_tiled_finish_rows", "dis_tiled_end",
 ]
 
 
@@ -290,6 +294,107 @@ class Engine:
         s = DisStats()
         _chk(self.lib.dis_get_stats(self._h, C.byref(s)))
         return {n: int(getattr(s, n)) for n, _ in DisStats._fields_}
+
+
+class Pool:
+    """Several GPUs behind one handle (dis_pool_*): one engine + host thread per device, pairs sharded contiguously,
+    no collective (/root/reference/src/main.cpp:102 — the loop body shares no state between pairs)."""
+
+    def __init__(self, devices, **params):
+        self.lib = load_library()
+        self.lib.dis_pool_last_error.restype = C.c_char_p
+        self.lib.dis_pool_destroy.restype = None
+        self.lib.dis_pool_destroy.argtypes = [C.c_void_p]
+        self.params = default_params(**params)
+        self.devices = [int(d) for d in devices]
+        self._h = C.c_void_p()
+        dv = (C.c_int * len(self.devices))(*self.devices)
+        self._chk(self.lib.dis_pool_create(C.byref(self.params), dv, len(self.devices), C.byref(self._h)))
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise DisError(f"dis_b200 pool error {rc}: {self.lib.dis_pool_last_error().decode()}")
+
+    def close(self):
+        if self._h:
+            self.lib.dis_pool_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def run_sequence(self, frames: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n, h, w = frames.shape
+        if out is None:
+            out = np.empty((n - 1, h, w, 2), np.float32)
+        self._chk(self.lib.dis_pool_run_sequence_u8(self._h, frames.ctypes.data_as(_u8p), n, w, h, w, C.c_size_t(h * w),
+                                                    out.ctypes.data_as(_fp)))
+        return out
+
+    def run_sequence_ptr(self, frames_ptr: int, n: int, w: int, h: int, out_ptr: int) -> None:
+        self._chk(self.lib.dis_pool_run_sequence_u8(self._h, C.cast(C.c_void_p(frames_ptr), _u8p), n, w, h, w, C.c_size_t(h * w),
+                                                    C.cast(C.c_void_p(out_ptr), _fp)))
+
+    def run_batch(self, a: np.ndarray, b: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        n, h, w = a.shape
+        if out is None:
+            out = np.empty((n, h, w, 2), np.float32)
+        pa = (C.c_void_p * n)(*[a.ctypes.data + i * h * w for i in range(n)])
+        pb = (C.c_void_p * n)(*[b.ctypes.data + i * h * w for i in range(n)])
+        self._chk(self.lib.dis_pool_run_batch_u8(self._h, pa, pb, n, w, h, w, out.ctypes.data_as(_fp)))
+        return out
+
+    def run_pair_tiled(self, a: np.ndarray, b: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """One large pair over all the pool's GPUs: bands of grid rows + per-level halo exchange over peer memory."""
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        h, w = a.shape
+        if out is None:
+            out = np.empty((h, w, 2), np.float32)
+        self._chk(self.lib.dis_pool_run_pair_tiled_u8(self._h, a.ctypes.data_as(_u8p), b.ctypes.data_as(_u8p), w, h, w,
+                                                      out.ctypes.data_as(_fp)))
+        return out
+
+    def run_pair_tiled_ptr(self, a_ptr: int, b_ptr: int, w: int, h: int, out_ptr: int) -> None:
+        self._chk(self.lib.dis_pool_run_pair_tiled_u8(self._h, C.cast(C.c_void_p(a_ptr), _u8p), C.cast(C.c_void_p(b_ptr), _u8p),
+                                                      w, h, w, C.cast(C.c_void_p(out_ptr), _fp)))
+
+    def run_batch_ptr(self, a_ptr: int, b_ptr: int, n: int, w: int, h: int, out_ptr: int) -> None:
+        """n pairs stored back to back at a_ptr / b_ptr (e.g. pinned host memory)."""
+        pa = (C.c_void_p * n)(*[a_ptr + i * h * w for i in range(n)])
+        pb = (C.c_void_p * n)(*[b_ptr + i * h * w for i in range(n)])
+        self._chk(self.lib.dis_pool_run_batch_u8(self._h, pa, pb, n, w, h, w, C.cast(C.c_void_p(out_ptr), _fp)))
+
+    def stats(self) -> dict:
+        s = DisStats()
+        self._chk(self.lib.dis_pool_get_stats(self._h, C.byref(s)))
+        return {n: int(getattr(s, n)) for n, _ in DisStats._fields_}
+
+    def last_ms(self):
+        wall = C.c_double()
+        per = (C.c_double * len(self.devices))()
+        self._chk(self.lib.dis_pool_last_ms(self._h, C.byref(wall), per))
+        return float(wall.value), [float(x) for x in per]
+
+    def workers(self):
+        out = []
+        for i in range(len(self.devices)):
+            d, n = C.c_int(), C.c_int()
+            self._chk(self.lib.dis_pool_device(self._h, i, C.byref(d), C.byref(n)))
+            out.append({"device": int(d.value), "numa_cpus": int(n.value)})
+        return out
+
+    def host_alloc(self, worker: int, nbytes: int) -> int:
+        p = C.c_void_p()
+        self._chk(self.lib.dis_pool_host_alloc(self._h, int(worker), C.c_size_t(nbytes), C.byref(p)))
+        return int(p.value)
+
+    def host_free(self, ptr: int) -> None:
+        self._chk(self.lib.dis_pool_host_free(self._h, C.c_void_p(ptr)))
 
 
 def write_flo(path: str, flow: np.ndarray) -> None:

@@ -3,4 +3,4 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 import this package.  The product package never does.
 """
-from .binding import Oracle, build, load_port, load_ref  # noqa: F401
+from .binding import Oracle, RefViz, build, load_port, load_ref, load_refviz  # noqa: F401

@@ -12,6 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _PORT = os.path.join(_HERE, "libdis_oracle.so")
 _REF = os.path.join(_HERE, "_ref", "libdis_ref.so")
+_REFVIZ = os.path.join(_HERE, "_ref", "libdis_refviz.so")
 _fpp = C.POINTER(C.POINTER(C.c_float))
 _fp = C.POINTER(C.c_float)
 
@@ -37,6 +38,41 @@ def load_ref():
     lib = C.CDLL(_REF)
     assert lib.ref_new_is_zeroing() == 1, "zero-filling operator new[] not bound inside libdis_ref.so"
     return lib
+
+
+def load_refviz():
+    """The reference's own colour coding + .flo I/O (src/color_coding.cpp, src/IO_flow.cpp compiled unmodified), or None."""
+    if not os.path.exists(_REFVIZ):
+        if os.path.isdir("/root/reference/src"):
+            build(ref=True)
+        else:
+            return None
+    return C.CDLL(_REFVIZ)
+
+
+class RefViz:
+    """draw_optical_flow / SaveFlowFile / ReadFlowFile of the reference itself."""
+
+    def __init__(self):
+        self.lib = load_refviz()
+        if self.lib is None:
+            raise RuntimeError("oracle/_ref/libdis_refviz.so not available")
+
+    def color_code(self, flow, maxmotion=-1.0):
+        flow = np.ascontiguousarray(flow, np.float32)
+        h, w, _ = flow.shape
+        out = np.empty((h, w, 3), np.uint8)
+        self.lib.ref_color_code(flow.ctypes.data_as(_fp), w, h, C.c_float(maxmotion), out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def save_flo(self, path, flow):
+        flow = np.ascontiguousarray(flow, np.float32)
+        self.lib.ref_save_flo(flow.ctypes.data_as(_fp), flow.shape[1], flow.shape[0], str(path).encode())
+
+    def read_flo(self, path, w, h):
+        out = np.zeros((h, w, 2), np.float32)
+        self.lib.ref_read_flo(str(path).encode(), out.ctypes.data_as(_fp), w, h)
+        return out
 
 
 def _ptrs(arrs):

@@ -121,33 +121,30 @@ def test_img_padding_larger_than_patch_size(eng, oracle_port):
     assert np.array_equal(bits(eng.run_pyramids(pa, pb, 11, W, H)), bits(ref))
 
 
-def test_finest_scale_epilogue(oracle_port):
-    """finest_scale = 1: the engine stops one level early, then flow*2 and a x2 bilinear upsample
-    (src/main.cpp:192-196).  The level flow is parity-gated bit for bit; the upsample against a
-    float64 restatement of cv::resize INTER_LINEAR within 1e-5 px."""
-    a, b, _ = dis_b200.synth.make_pair(256, 112, seed=44)
-    e = dis_b200.Engine(0, finest_scale=1)
+@pytest.mark.parametrize("w,h,finest,coarsest", [(256, 112, 1, 3), (250, 107, 1, 3), (320, 200, 2, 3), (200, 100, 3, 3)])
+def test_finest_scale_epilogue_equals_cv2_resize(oracle_port, w, h, finest, coarsest):
+    """finest_scale > 0: the engine stops early, then flow * 2^f, a x2^f INTER_LINEAR upsample and the crop of the
+    divisibility padding (src/main.cpp:192-198).  The level flow is parity-gated bit for bit against the oracle; the
+    epilogue against OpenCV ITSELF (cv2.resize, optimised paths off), bit for bit — ragged sizes (crop offsets) and
+    scales 2, 4, 8 included."""
+    cv2 = pytest.importorskip("cv2")
+    cv2.setUseOptimized(False)
+    cv2.setNumThreads(1)
+    a, b, _ = dis_b200.synth.make_pair(w, h, seed=44)
+    e = dis_b200.Engine(0, finest_scale=finest, coarsest_scale=coarsest, max_iter=40)
     try:
         out = e.run_pair(a, b)
-        _, d = oracle_port.run_pair_u8(a, b, finest=1, dump=True)
         lf = e.level_flow(0, 0)
-        assert np.array_equal(bits(lf), bits(d["flow"][0]))
-        Hf, Wf = lf.shape[:2]
-        ys = (np.arange(2 * Hf) + 0.5) / 2 - 0.5
-        xs = (np.arange(2 * Wf) + 0.5) / 2 - 0.5
-        y0 = np.clip(np.floor(ys).astype(int), 0, Hf - 1); y1 = np.clip(y0 + 1, 0, Hf - 1)
-        x0 = np.clip(np.floor(xs).astype(int), 0, Wf - 1); x1 = np.clip(x0 + 1, 0, Wf - 1)
-        ay = np.clip(ys - np.floor(ys), 0, 1) * (ys >= 0) * (ys <= Hf - 1)
-        ax = np.clip(xs - np.floor(xs), 0, 1) * (xs >= 0) * (xs <= Wf - 1)
-        f = lf.astype(np.float64) * 2
-        top = f[y0][:, x0] * (1 - ax)[None, :, None] + f[y0][:, x1] * ax[None, :, None]
-        bot = f[y1][:, x0] * (1 - ax)[None, :, None] + f[y1][:, x1] * ax[None, :, None]
-        up = top * (1 - ay)[:, None, None] + bot * ay[:, None, None]
-        exp = up                      # 256x112 needs no divisibility padding, so the crop is the identity
-        assert out.shape == (112, 256, 2)
-        assert np.abs(out - exp).max() < 1e-5
     finally:
         e.close()
+    _, d = oracle_port.run_pair_u8(a, b, finest=finest, coarsest=coarsest, iterations=40, dump=True)
+    assert np.array_equal(bits(lf), bits(d["flow"][0]))
+    sc = 1 << finest
+    up = cv2.resize(lf * np.float32(sc), None, fx=sc, fy=sc, interpolation=cv2.INTER_LINEAR)    # main.cpp:193-195
+    pw, ph = oracle_port.div_pad(w, coarsest), oracle_port.div_pad(h, coarsest)
+    exp = up[ph // 2:ph // 2 + h, pw // 2:pw // 2 + w]                                           # main.cpp:198
+    assert out.shape == (h, w, 2)
+    assert np.array_equal(bits(out), bits(np.ascontiguousarray(exp)))
 
 
 def test_colour_coding_matches_oracle(eng, oracle_port):
@@ -156,6 +153,11 @@ def test_colour_coding_matches_oracle(eng, oracle_port):
     a, b, _ = dis_b200.synth.make_pair(256, 112, seed=9)
     flow = eng.run_pair(a, b)
     ref = oracle_port.color_code(flow)
+    import oracle
+    if oracle.load_refviz() is not None:     # the reference's own src/color_coding.cpp, compiled unmodified (oracle/_ref)
+        rv = oracle.RefViz()
+        assert np.array_equal(eng.color_code(flow), rv.color_code(flow))
+        assert np.array_equal(eng.color_code(flow, 1.5), rv.color_code(flow, 1.5))
     assert np.array_equal(eng.color_code(flow), ref)
     assert np.array_equal(eng.color_code_pair(0, 112, 256), ref)
     assert np.array_equal(eng.color_code(flow, 1.5), oracle_port.color_code(flow, 1.5))

@@ -38,7 +38,8 @@ def test_hq_1920x1080_patch12_matches_oracle(oracle_port):
 
 
 def test_4k_3840x2160_matches_oracle(oracle_port):
-    """config 5 geometry on one GPU (the row-tiled multi-GPU variant is not built): 2 754 000 patches."""
+    """config 5 geometry on one GPU: 2 754 000 patches (the row-tiled multi-GPU variants — NCCL all-gather between processes,
+    halo exchange over peer memory inside one process — are covered by tests/test_gpu_tiled.py)."""
     a, b, _ = dis_b200.synth.make_pair(3840, 2160, seed=1, amp=11.0)
     e = dis_b200.Engine(0, max_iter=26)
     try:

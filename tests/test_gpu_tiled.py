@@ -112,3 +112,69 @@ def test_tiled_over_nccl_when_two_gpus_are_present():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert res == [(0, True), (1, True)]
+
+
+# ---- the in-process path: dis_pool_run_pair_tiled_u8 — bands of grid rows, HALO exchange over peer memory, every GPU
+#      densifies and downloads only its own band (csrc/dis_pool.cu) ------------------------------------------------------
+def pool_device_lists(n):
+    import torch
+    out = [[0] * n]                                   # n engines on one GPU: the exchange degenerates to local copies
+    if torch.cuda.device_count() >= n > 1:
+        out.append(list(range(n)))                    # real peers over NVLink
+    return out
+
+
+@pytest.mark.parametrize("world,w,h,kw", [
+    (1, 256, 112, {}),
+    (2, 512, 256, {}),
+    (3, 250, 107, dict(max_iter=40)),                                   # ragged size, bands of unequal height
+    (4, 480, 272, dict(patch_size=12, patch_overlap=0.75, coarsest_scale=2, max_iter=60)),
+    (8, 128, 64, dict(max_iter=30)),                                    # more GPUs than grid rows at the coarsest level
+    (5, 200, 100, dict(patch_size=4, max_iter=25)),
+])
+def test_pool_tiled_halo_exchange_matches_single_engine(world, w, h, kw):
+    a, b, _ = dis_b200.synth.make_pair(w, h, seed=33, amp=4.0)
+    single = dis_b200.Engine(0, **kw)
+    try:
+        ref = single.run_pair(a, b)
+        st_ref = single.stats()
+    finally:
+        single.close()
+    for devs in pool_device_lists(world):
+        p = dis_b200.Pool(devs, **kw)
+        try:
+            out = p.run_pair_tiled(a, b)
+            assert np.array_equal(bits(out), bits(ref)), f"devices {devs}"
+            again = p.run_pair_tiled(a, b)
+            assert np.array_equal(bits(again), bits(ref)), f"second run, devices {devs}"
+            st = p.stats()
+            # the bands partition the patches and the iteration counters add up to the single-engine run
+            assert st["patches"] == st_ref["patches"] and st["patch_iterations"] == st_ref["patch_iterations"]
+        finally:
+            p.close()
+
+
+def test_pool_tiled_4k_matches_single_engine():
+    """config 5 shape, three bands, a budget that crosses the walk hand-off."""
+    a, b, _ = dis_b200.synth.make_pair(3840, 2160, seed=2, amp=11.0)
+    single = dis_b200.Engine(0, max_iter=30)
+    try:
+        ref = single.run_pair(a, b)
+    finally:
+        single.close()
+    for devs in pool_device_lists(3):
+        p = dis_b200.Pool(devs, max_iter=30)
+        try:
+            assert np.array_equal(bits(p.run_pair_tiled(a, b)), bits(ref)), f"devices {devs}"
+        finally:
+            p.close()
+
+
+def test_pool_tiled_rejects_finest_scale():
+    a, b, _ = dis_b200.synth.make_pair(128, 64, seed=1)
+    p = dis_b200.Pool([0, 0], finest_scale=1)
+    try:
+        with pytest.raises(dis_b200.DisError):
+            p.run_pair_tiled(a, b)
+    finally:
+        p.close()

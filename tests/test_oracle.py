@@ -144,3 +144,44 @@ def test_colour_coding_known_answers(oracle_port):
     assert c[1, 0].tolist() == [255, 255, 0] or c[1, 0][2] == 0          # opposite direction: cyan side of the wheel
     d = oracle_port.color_code(f, maxmotion=0.5)                          # radius 2 > 1: colour * 0.75
     assert d[0, 1].tolist() == [0, 0, 191]
+
+
+# ---- N1 / N2 pinned against the reference ITSELF: src/color_coding.cpp and src/IO_flow.cpp compiled unmodified where
+#      they lie against a functional miniature of the cv types they use (oracle/stubs_cv, oracle/_ref/libdis_refviz.so) ----
+@pytest.fixture(scope="module")
+def refviz():
+    import oracle
+    if oracle.load_refviz() is None:
+        pytest.skip("oracle/_ref/libdis_refviz.so not built (no /root/reference here)")
+    return oracle.RefViz()
+
+
+def viz_fields(oracle_port):
+    rng = np.random.default_rng(0)
+    out = [(rng.standard_normal((h, w, 2)) * s).astype(np.float32) for w, h, s in ((64, 48, 1.0), (200, 100, 3.0), (333, 77, 0.2), (128, 64, 30.0))]
+    a, b, gt = dis_b200.synth.make_pair(256, 112, seed=1)
+    out += [oracle_port.run_pair_u8(a, b, iterations=30), gt.copy()]
+    f = out[0].copy(); f[3, 4, 0] = np.nan; f[5, 6, 1] = 2e9; f[0, 0] = 0; f[7, 7] = (np.inf, 1)
+    out.append(f)
+    out.append(np.zeros((5, 9, 2), np.float32))
+    return out
+
+
+def test_colour_coding_port_equals_the_reference(oracle_port, refviz):
+    """oracle_color_code (the restatement the GPU kernel is tested against) == draw_optical_flow of the reference's own
+    src/color_coding.cpp:83-117, byte for byte, for automatic and fixed ranges, invalid vectors included."""
+    for f in viz_fields(oracle_port):
+        for mm in (-1.0, 0.0, 2.5):
+            assert np.array_equal(oracle_port.color_code(f, mm), refviz.color_code(f, mm)), (f.shape, mm)
+
+
+def test_flo_files_equal_the_reference(oracle_port, refviz, tmp_path):
+    """dis_write_flo writes the bytes SaveFlowFile writes (src/IO_flow.cpp:58-98); each side reads the other's file."""
+    for i, f in enumerate(viz_fields(oracle_port)[:6]):
+        h, w, _ = f.shape
+        mine, theirs = tmp_path / f"m{i}.flo", tmp_path / f"r{i}.flo"
+        dis_b200.write_flo(str(mine), f)
+        refviz.save_flo(theirs, f)
+        assert open(mine, "rb").read() == open(theirs, "rb").read()
+        assert np.array_equal(bits(dis_b200.read_flo(str(theirs))), bits(f))
+        assert np.array_equal(bits(refviz.read_flo(mine, w, h)), bits(f))

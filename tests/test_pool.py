@@ -1,0 +1,92 @@
+"""dis_pool_*: several GPUs of one box behind one handle — the pair loop of /root/reference/src/main.cpp:102 sharded over
+devices (contiguous blocks, one shared frame between neighbouring blocks of a sequence, no collective).  The sharding
+rule is checked on the CPU; the GPU tests run two engines on ONE GPU (devices [0, 0]) so that the pool is exercised on a
+single-GPU box too, and two different GPUs where the box has them."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import dis_b200
+
+
+def test_pool_shard_rule_matches_the_python_plumbing():
+    lib = dis_b200.load_library()
+    lib.dis_pool_shard.restype = None
+    for n in (0, 1, 2, 7, 49, 50, 4096):
+        for parts in (1, 2, 3, 4, 8):
+            prev = 0
+            for r in range(parts):
+                lo, hi = C.c_int(), C.c_int()
+                lib.dis_pool_shard(n, parts, r, C.byref(lo), C.byref(hi))
+                assert (lo.value, hi.value) == dis_b200.parallel.shard_pairs(n, parts, r)
+                assert lo.value == prev
+                prev = hi.value
+            assert prev == n
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def seq():
+    frames, _ = dis_b200.synth.make_sequence(12, 200, 100, seed=21)
+    e = dis_b200.Engine(0)
+    ref = e.run_sequence(frames)
+    st = e.stats()
+    e.close()
+    return frames, ref, st
+
+
+def devices_for_test():
+    import torch
+    out = [[0, 0], [0, 0, 0]]
+    if torch.cuda.device_count() >= 2:
+        out.append([0, 1])
+    if torch.cuda.device_count() >= 4:
+        out.append([0, 1, 2, 3])
+    return out
+
+
+@pytest.mark.gpu
+def test_pool_sequence_and_batch_equal_one_engine(seq):
+    frames, ref, st = seq
+    for devs in devices_for_test():
+        p = dis_b200.Pool(devs)
+        try:
+            out = p.run_sequence(frames)
+            assert np.array_equal(bits(out), bits(ref)), f"sequence over devices {devs}"
+            ps = p.stats()
+            assert ps["patches"] == st["patches"] and ps["patch_iterations"] == st["patch_iterations"]
+            wall, per = p.last_ms()
+            assert wall > 0 and len(per) == len(devs) and all(x > 0 for x in per)
+            outb = p.run_batch(frames[:-1], frames[1:])
+            assert np.array_equal(bits(outb), bits(ref)), f"batch over devices {devs}"
+            assert [w["device"] for w in p.workers()] == devs
+            # fewer pairs than workers: some workers get nothing
+            few = p.run_sequence(frames[:2])
+            assert np.array_equal(bits(few[0]), bits(ref[0]))
+        finally:
+            p.close()
+
+
+@pytest.mark.gpu
+def test_pool_pinned_buffers_and_errors(seq):
+    frames, ref, _ = seq
+    n, h, w = frames.shape
+    p = dis_b200.Pool([0, 0])
+    try:
+        src = p.host_alloc(0, frames.nbytes)
+        dst = p.host_alloc(1, ref.nbytes)
+        C.memmove(src, frames.ctypes.data, frames.nbytes)
+        p.run_sequence_ptr(src, n, w, h, dst)
+        got = np.ctypeslib.as_array(C.cast(dst, C.POINTER(C.c_float)), shape=ref.shape)
+        assert np.array_equal(bits(got), bits(ref))
+        p.host_free(src); p.host_free(dst)
+        with pytest.raises(dis_b200.DisError):
+            p.run_sequence(frames[:1])
+    finally:
+        p.close()
+    with pytest.raises(dis_b200.DisError):
+        dis_b200.Pool([99])
