@@ -229,6 +229,7 @@ def main():
     ap.add_argument("--max-iter", type=int, default=1000)
     ap.add_argument("--no-numa-bind", action="store_true")
     ap.add_argument("--no-config3", action="store_true")
+    ap.add_argument("--no-tiled", action="store_true")
     ap.add_argument("--ref-strip", type=int, default=0, help="reference arm: crop pairs to their top H rows (0 = whole pairs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -373,6 +374,54 @@ def main():
                 "patch_iterations_per_step": fst["patch_iterations"],
                 "note": "stops a patch once |delta_u| < conv_eps; within the 0.01 px dense gate, misses the 99.9 % per-patch gate (SURVEY.md App. B)"}
 
+    # ---- BASELINE config 5: ONE 3840x2160 pair split over the N GPUs by bands of grid rows, halo exchange over NVLink
+    #      peer memory (dis_pool_run_pair_tiled_u8).  In-process: rank 0 drives all N GPUs, the other ranks wait. -----------
+    tiled = None
+    if world > 1 and not args.no_tiled:
+        barrier()
+        if rank == 0:
+            try:
+                a4, b4, _ = dis_b200.synth.make_pair(3840, 2160, seed=500, amp=11.0)
+                one = dis_b200.Engine(local_rank, max_iter=args.max_iter)
+                pa = torch.from_numpy(a4).pin_memory(); pb = torch.from_numpy(b4).pin_memory()
+                po1 = torch.empty((2160, 3840, 2), dtype=torch.float32).pin_memory()
+                poN = torch.empty((2160, 3840, 2), dtype=torch.float32).pin_memory()
+                lib = dis_b200.load_library()
+                import ctypes as C
+
+                def single():
+                    rc = lib.dis_run_pair_u8(one._h, C.c_void_p(pa.data_ptr()), C.c_void_p(pb.data_ptr()), 3840, 2160, 3840, C.c_void_p(po1.data_ptr()))
+                    assert rc == 0
+                single()
+                t0 = time.perf_counter()
+                for _ in range(3):
+                    single()
+                one_ms = (time.perf_counter() - t0) / 3 * 1e3
+                one.upload_frames(np.stack([a4, b4]), np.array([0], np.int32), np.array([1], np.int32))
+                one.run_resident(); one.synchronize(); one.timer_start()
+                for _ in range(3):
+                    one.run_resident()
+                one_dev_ms = one.timer_stop_ms() / 3
+                one.close()
+                pool = dis_b200.Pool(list(range(world)), max_iter=args.max_iter)
+                pool.run_pair_tiled_ptr(pa.data_ptr(), pb.data_ptr(), 3840, 2160, poN.data_ptr())
+                t0 = time.perf_counter()
+                dev = []
+                for _ in range(3):
+                    pool.run_pair_tiled_ptr(pa.data_ptr(), pb.data_ptr(), 3840, 2160, poN.data_ptr())
+                    dev.append(pool.last_tiled_device_ms())
+                n_ms = (time.perf_counter() - t0) / 3 * 1e3
+                pool.close()
+                tiled = {"workload": "one synthetic 3840x2160 pair, defaults, max_iter %d, bands of grid rows + per-level halo exchange over peer memory" % args.max_iter,
+                         "n_gpus": world, "ms_per_pair_host_to_host": n_ms, "ms_per_pair_device": float(np.mean(dev)),
+                         "one_gpu_ms_per_pair_host_to_host": one_ms, "one_gpu_ms_per_pair_device": one_dev_ms,
+                         "speedup_host_to_host": one_ms / n_ms, "speedup_device": one_dev_ms / float(np.mean(dev)),
+                         "bit_identical_to_one_gpu": bool(np.array_equal(po1.numpy().view(np.uint32), poN.numpy().view(np.uint32)))}
+            except Exception as ex:  # noqa: BLE001
+                tiled = {"error": str(ex)[:300]}
+            torch.cuda.set_device(local_rank)
+        barrier()
+
     # run counters summed over ranks (NCCL all-reduce; statistics only — no pixel data crosses ranks)
     job = dis_b200.parallel.reduce_stats(st, dev_ms, dist, "cuda")
     if rank == 0:
@@ -443,7 +492,7 @@ def main():
                  "ms_per_level_fine_to_coarse": phase_ms[1]},
                 {"kernel": "k_stragglers<8,4>", "ms_per_step_not_hidden_by_the_walk": strag_ms, "sampled_passes": s_strag,
                  "ms_per_level_fine_to_coarse": phase_ms[2]}],
-            "config3_4096_pairs": config3, "per_rank_copy_rates": all_rates,
+            "config3_4096_pairs": config3, "tiled_4k": tiled, "per_rank_copy_rates": all_rates,
             "stats_per_step": st, "stats_job_per_step": job, "search_share_of_step": search_ms / step_ms,
             "clocks": clocks, "checksum": checksum,
         }

@@ -222,6 +222,9 @@ DIS_API int dis_tiled_fetch_u_rows(dis_engine* e, int level, dis_engine* src, in
 DIS_API int dis_tiled_densify_rows(dis_engine* e, int level, int y0, int y1);
 DIS_API int dis_tiled_finish_rows(dis_engine* e, float* flow_out, int y0, int y1);
 DIS_API int dis_tiled_end(dis_engine* e);
+/* device time (CUDA events on e's stream) of the last halo-exchange run on this engine: pyramids + all levels, from
+ * after the upload was enqueued to before the download */
+DIS_API int dis_tiled_last_ms(dis_engine* e, float* ms);
 
 /* ---- several GPUs of one box behind one handle ------------------------------------------------------------------
  * The reference's unit of independent work is one iteration of its per-pair loop (src/main.cpp:102; the body shares no
@@ -251,6 +254,9 @@ DIS_API int dis_pool_run_sequence_u8(dis_pool* pool, const uint8_t* frames, int 
  * its band of the output) and downloads only that band.  Bit-identical to dis_run_pair_u8.  finest_scale must be 0. */
 DIS_API int dis_pool_run_pair_tiled_u8(dis_pool* pool, const uint8_t* a, const uint8_t* b, int w, int h, int stride,
                                        float* flow_out);
+/* device time of the last dis_pool_run_pair_tiled_u8: the slowest GPU's pyramids + levels (CUDA events), i.e. the run
+ * without its host<->device copies */
+DIS_API int dis_pool_last_tiled_device_ms(dis_pool* pool, double* max_ms);
 DIS_API int dis_pool_get_stats(dis_pool* pool, dis_stats* sum);                              /* summed over the devices of the last call */
 DIS_API int dis_pool_last_ms(dis_pool* pool, double* wall_ms, double* per_worker_ms);        /* host wall clock of the last call */
 DIS_API int dis_pool_host_alloc(dis_pool* pool, int worker, size_t bytes, void** out);       /* pinned, NUMA-local to that worker's GPU */

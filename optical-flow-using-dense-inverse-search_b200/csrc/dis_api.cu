@@ -13,10 +13,22 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges cost nothing unless a tool (nsys, ncu --nvtx) is attached
+
 #include "../../include/dis_b200.h"
 #include "dis_kernels.cuh"
 
 namespace {
+
+// NVTX ranges around the stages of a run (the reference's only trace is `cout << "scale: N"`, src/optical_flow.cpp:69):
+// "dis.pyramids", "dis.level<scale>.search" (k_converge + walk + k_stragglers), "dis.level<scale>.densify",
+// "dis.epilogue", "dis.upload", "dis.download".  Host-side ranges around asynchronous launches: a tool's CUDA
+// projection maps them onto the kernels.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  NvtxRange(const char* fmt, int a) { char b[64]; snprintf(b, sizeof b, fmt, a); nvtxRangePushA(b); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 thread_local std::string g_err;
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
@@ -83,6 +95,8 @@ struct dis_engine {
   std::vector<cudaEvent_t> tiled_ev;    // per level: "this engine's band of the level has been searched" (row-banded runs)
   int2 tiled_pr = {0, 1};               // the pair record of a tiled run (outlives the asynchronous upload)
   unsigned long long tiled_patches = 0; // patches this engine searched in the current tiled run
+  cudaEvent_t tiled_t0 = nullptr, tiled_t1 = nullptr;   // device time of a row-banded run: after the upload .. before the download
+  float tiled_ms = 0.f;
   bool stats_fetched = false;
   bool out_sent = false;                // the last run already copied its flows to the caller's buffer
   bool keep_iters = true;
@@ -301,10 +315,17 @@ int run_levels_group(dis_engine* e, int g, int p0, int p1, cudaStream_t st, floa
     for (int c = 0; c < slices; ++c) {
       const int q0 = cut[c], q1 = cut[c + 1];
       const dis::SearchArgs a = level_search_args(e, g, s, q0, q1);
-      const int n = dis::launch_inverse_search(a, e->prm.patch_size, st, c == 0 ? ev : nullptr, side);   // timings: first slice only
+      int n;
+      {
+        NvtxRange r("dis.level%d.search", e->levels[s].info.scale);
+        n = dis::launch_inverse_search(a, e->prm.patch_size, st, c == 0 ? ev : nullptr, side);   // timings: first slice only
+      }
       if (n < 0) return fail(DIS_ERR_PARAM, "unsupported patch_size");
       e->launches += n;
-      level_densify(e, s, q0, q1, st);
+      {
+        NvtxRange r("dis.level%d.densify", e->levels[s].info.scale);
+        level_densify(e, s, q0, q1, st);
+      }
       if (s == 0 && host_out) {
         if (int rc = run_epilogue(e, q0, q1)) return rc;
         const size_t off = 2 * (size_t)e->w0 * e->h0 * q0, cnt = 2 * (size_t)e->w0 * e->h0 * (q1 - q0);
@@ -392,6 +413,7 @@ int run_pyramid_u8(dis_engine* e, int stride) {
   a.W = e->W; a.H = e->H; a.left = e->left; a.top = e->top;
   a.n_frames = e->n_frames; a.levels = e->prm.coarsest_scale + 1; a.pad = e->pad;
   for (int s = 0; s <= e->prm.coarsest_scale; ++s) a.planes[s] = e->planes[s];
+  NvtxRange r("dis.pyramids");
   e->launches += dis::launch_pyramid(a, e->stream);
   CU(cudaGetLastError());
   return DIS_OK;
@@ -399,6 +421,7 @@ int run_pyramid_u8(dis_engine* e, int stride) {
 
 // finest dense flow -> cropped output (src/main.cpp:192-198), device to device, pairs [p0, p1)
 int run_epilogue(dis_engine* e, int p0, int p1) {
+  NvtxRange r("dis.epilogue");
   Level& L = e->levels[0];
   if (e->out.ensure(sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
   const float* dense = L.flow.as<float>() + L.flow_stride * p0;
@@ -1079,6 +1102,9 @@ int dis_tiled_begin(dis_engine* e, const uint8_t* a, const uint8_t* b, int w, in
   CU(cudaMemcpyAsync(e->pairs.p, &e->tiled_pr, sizeof e->tiled_pr, cudaMemcpyHostToDevice, e->stream));
   e->stride_u8 = w;
   e->launches = 0;
+  if (!e->tiled_t0) { CU(cudaEventCreate(&e->tiled_t0)); CU(cudaEventCreate(&e->tiled_t1)); }
+  CU(cudaEventRecord(e->tiled_t0, e->stream));
+  CU(cudaEventRecord(e->tiled_t1, e->stream));
   if (int rc = run_pyramid_u8(e, w)) return rc;
   CU(cudaMemsetAsync(e->counters.p, 0, dis::kCounters * sizeof(unsigned long long), e->stream));
   for (Level& L : e->levels)   // patches outside this GPU's bands are filled in by dis_tiled_set_u
@@ -1155,8 +1181,9 @@ int dis_tiled_finish_rows(dis_engine* e, float* flow_out, int y0, int y1) {
   if (!e->tiled) return fail(DIS_ERR_STATE, "dis_tiled_begin first");
   if (e->prm.finest_scale != 0) return fail(DIS_ERR_PARAM, "row-banded download needs finest_scale == 0");
   if (y0 < 0 || y1 > e->h0 || y0 > y1) return fail(DIS_ERR_PARAM, "output rows out of range");
-  if (y0 == y1) return DIS_OK;
   CU(cudaSetDevice(e->device));
+  CU(cudaEventRecord(e->tiled_t1, e->stream));
+  if (y0 == y1) return DIS_OK;
   Level& L = e->levels[0];
   const size_t row = 2 * (size_t)e->w0;
   if (e->out.ensure(sizeof(float) * row * e->h0)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
@@ -1173,7 +1200,16 @@ int dis_tiled_end(dis_engine* e) {
   CU(cudaSetDevice(e->device));
   e->stats.patches = e->tiled_patches;   // this engine's bands; the counters below are its share too
   e->have_run = true; e->stats_fetched = false; e->tiled = false;
-  return fetch_counters(e);           // synchronises the stream
+  const int rc = fetch_counters(e);      // synchronises the stream
+  e->tiled_ms = 0.f;
+  if (!rc && e->tiled_t0) { if (cudaEventElapsedTime(&e->tiled_ms, e->tiled_t0, e->tiled_t1) != cudaSuccess) { cudaGetLastError(); e->tiled_ms = 0.f; } }
+  return rc;
+}
+
+int dis_tiled_last_ms(dis_engine* e, float* ms) {
+  if (!e || !ms) return fail(DIS_ERR_PARAM, "null argument");
+  *ms = e->tiled_ms;
+  return DIS_OK;
 }
 
 static int tiled_copy_u(dis_engine* e, int level, void* dst, const void* src, bool get) {

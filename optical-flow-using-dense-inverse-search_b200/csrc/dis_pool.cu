@@ -272,6 +272,11 @@ int dis_pool_run_pair_tiled_u8(dis_pool* p, const uint8_t* a, const uint8_t* b, 
   if (p->prm.finest_scale != 0) return pfail(DIS_ERR_PARAM, "the row-banded path needs finest_scale == 0");
   const int R = (int)p->w.size();
   const auto t0 = std::chrono::steady_clock::now();
+  struct DeviceGuard {   // this function issues work to every GPU from the caller's thread: leave its current device as it was
+    int dev = -1;
+    DeviceGuard() { if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = -1; } }
+    ~DeviceGuard() { if (dev >= 0) cudaSetDevice(dev); }
+  } guard;
   // peer access between every two distinct devices of the pool (once)
   if (!p->peers_ready) {
     for (int i = 0; i < R; ++i)
@@ -349,6 +354,14 @@ int dis_pool_run_pair_tiled_u8(dis_pool* p, const uint8_t* a, const uint8_t* b, 
   }
   p->wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return rc ? pfail(rc, err) : DIS_OK;
+}
+
+int dis_pool_last_tiled_device_ms(dis_pool* p, double* max_ms) {
+  if (!p || !max_ms) return pfail(DIS_ERR_PARAM, "null argument");
+  double m = 0;
+  for (Worker* w : p->w) { float ms = 0.f; dis_tiled_last_ms(w->eng, &ms); if (ms > m) m = ms; }
+  *max_ms = m;
+  return DIS_OK;
 }
 
 int dis_pool_get_stats(dis_pool* p, dis_stats* out) {

@@ -56,7 +56,7 @@ ABI_SYMBOLS = [
     "dis_pool_create", "dis_pool_destroy", "dis_pool_size", "dis_pool_device", "dis_pool_last_error", "dis_pool_shard",
     "dis_pool_run_batch_u8", "dis_pool_run_sequence_u8", "dis_pool_get_stats", "dis_pool_last_ms", "dis_pool_host_alloc",
     "dis_pool_host_free", "dis_pool_run_pair_tiled_u8", "dis_tiled_fetch_u_rows", "dis_tiled_densify_rows",
-    "dis_tiled_finish_rows", "dis_tiled_end",
+    "dis_tiled_finish_rows", "dis_tiled_end", "dis_tiled_last_ms", "dis_pool_last_tiled_device_ms",
 ]
 
 
@@ -358,6 +358,11 @@ class Pool:
         self._chk(self.lib.dis_pool_run_pair_tiled_u8(self._h, a.ctypes.data_as(_u8p), b.ctypes.data_as(_u8p), w, h, w,
                                                       out.ctypes.data_as(_fp)))
         return out
+
+    def last_tiled_device_ms(self) -> float:
+        ms = C.c_double()
+        self._chk(self.lib.dis_pool_last_tiled_device_ms(self._h, C.byref(ms)))
+        return float(ms.value)
 
     def run_pair_tiled_ptr(self, a_ptr: int, b_ptr: int, w: int, h: int, out_ptr: int) -> None:
         self._chk(self.lib.dis_pool_run_pair_tiled_u8(self._h, C.cast(C.c_void_p(a_ptr), _u8p), C.cast(C.c_void_p(b_ptr), _u8p),

@@ -15,10 +15,18 @@ sys.path.insert(0, ROOT)
 def child(reps, n_frames):
     import numpy as np
     import dis_b200
-    frames, _ = dis_b200.synth.make_sequence(n_frames, 1024, 436, seed=100)
-    e = dis_b200.Engine(0)
-    first = np.arange(n_frames - 1, dtype=np.int32)
-    e.upload_frames(frames, first, first + 1)
+    if os.environ.get("EXP_HQ"):      # BASELINE config 4: 1920x1080, patch 12, overlap 0.75, scales 5->0; n_frames - 1 independent pairs
+        n = n_frames - 1
+        prs = [dis_b200.synth.make_pair(1920, 1080, seed=400 + i, amp=5.6)[:2] for i in range(n)]
+        frames = np.concatenate([np.stack([p[0] for p in prs]), np.stack([p[1] for p in prs])])
+        e = dis_b200.Engine(0, patch_size=12, patch_overlap=0.75, coarsest_scale=5)
+        first = np.arange(n, dtype=np.int32)
+        e.upload_frames(frames, first, first + n)
+    else:
+        frames, _ = dis_b200.synth.make_sequence(n_frames, 1024, 436, seed=100)
+        e = dis_b200.Engine(0)
+        first = np.arange(n_frames - 1, dtype=np.int32)
+        e.upload_frames(frames, first, first + 1)
     e.run_resident(); e.synchronize()
     e.timer_start()
     for _ in range(reps):
