@@ -378,6 +378,9 @@ def main():
     #      peer memory (dis_pool_run_pair_tiled_u8).  In-process: rank 0 drives all N GPUs, the other ranks wait. -----------
     tiled = None
     if world > 1 and not args.no_tiled:
+        # The other ranks must not wait INSIDE an NCCL collective while rank 0 drives their GPUs: a pending NCCL barrier is
+        # a kernel spinning on each of those GPUs (measured: it turns the 1.5x of two GPUs into 0.8x).  They wait on the CPU.
+        cpu_group = dist.new_group(backend="gloo")
         barrier()
         if rank == 0:
             try:
@@ -420,6 +423,7 @@ def main():
             except Exception as ex:  # noqa: BLE001
                 tiled = {"error": str(ex)[:300]}
             torch.cuda.set_device(local_rank)
+        dist.barrier(group=cpu_group)
         barrier()
 
     # run counters summed over ranks (NCCL all-reduce; statistics only — no pixel data crosses ranks)

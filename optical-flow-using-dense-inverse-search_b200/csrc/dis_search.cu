@@ -341,6 +341,41 @@ __device__ __forceinline__ float2 sample_window8(const Window8<SG>& Wn, float op
   return normalise_and_project<8, SG>(v, patnorm, T);
 }
 
+// Patch sizes other than 8: the four taps of each of the lane's elements, held in REGISTERS while the integer tap base
+// stays the same (it does for ~99 % of a patch's passes), so that a pass of k_converge / k_stragglers is arithmetic only.
+// The lane <-> element mapping stays Eigen's (e mod 8), which scatters a lane's elements over the patch: no taps are
+// shared between them, so this is 4 x NPL registers (72 at ps 12) — affordable up to ps 12.
+template <int PS, int SG>
+struct TapWindow {
+  static constexpr int NPL = Geom<PS, SG>::NPL;
+  float t[NPL][4];
+  int bx, by;
+  __device__ __forceinline__ void load(const float* __restrict__ imB, int tw, const int (&eoff)[NPL], int bxi, int byi) {
+    bx = bxi; by = byi;
+    const float* __restrict__ ib = imB + byi * tw + bxi;
+#pragma unroll
+    for (int i = 0; i < NPL; ++i) {
+      const float* p = ib + eoff[i];
+      t[i][0] = __ldg(p); t[i][1] = __ldg(p - 1); t[i][2] = __ldg(p - tw); t[i][3] = __ldg(p - tw - 1);
+    }
+  }
+};
+template <int PS, int SG>
+constexpr bool kUseTapWindow = PS != 8 && 4 * Geom<PS, SG>::NPL <= 72;
+
+template <int PS, int SG>
+__device__ __forceinline__ float2 sample_tapwindow(const TapWindow<PS, SG>& Wn, float opx, float opy, int patnorm,
+                                                   const float2 (&T)[Geom<PS, SG>::NPL]) {
+  using G = Geom<PS, SG>;
+  const float fl = floorf(opx), fk = floorf(opy);
+  const float a = opx - fl, b = opy - fk;
+  const float w0 = (1 - a) * (1 - b), w1 = a * (1 - b), w2 = b * (1 - a), w3 = a * b;
+  float v[G::NPL];
+#pragma unroll
+  for (int i = 0; i < G::NPL; ++i) v[i] = ((w3 * Wn.t[i][0] + w2 * Wn.t[i][1]) + w1 * Wn.t[i][2]) + w0 * Wn.t[i][3];
+  return normalise_and_project<PS, SG>(v, patnorm, T);
+}
+
 // ---- packed fp32 arithmetic -------------------------------------------------------------------------------------
 // sm_100a has packed fp32 instructions (PTX mul/fma.rn.f32x2, SASS FMUL2 / FFMA2): two IEEE round-to-nearest fp32
 // operations on a 64-bit register pair in ONE issue slot (the FP32 pipe is busy two cycles, so the flop rate is that
@@ -564,7 +599,11 @@ __device__ __forceinline__ float2 patch_init(const SearchArgs& A, int idx, int p
 #endif
 // ps <= 8: 8 warps x 2 blocks at <= 128 registers; larger patches keep more elements per lane and get the full register file
 __host__ __device__ constexpr int conv_warps(int ps) { return ps <= 8 ? DIS_CONV_WARPS : 4; }
-__host__ __device__ constexpr int conv_blocks(int ps) { return ps <= 8 ? DIS_CONV_BLOCKS : 1; }
+// ps 10 / 12 hold their tap window in registers (TapWindow): ~160 registers, three blocks of four warps per SM
+#ifndef DIS_BIG_BLOCKS
+#define DIS_BIG_BLOCKS 3
+#endif
+__host__ __device__ constexpr int conv_blocks(int ps) { return ps <= 8 ? DIS_CONV_BLOCKS : (ps <= 12 ? DIS_BIG_BLOCKS : 1); }
 template <int PS, int SG, bool FAST>
 __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_converge(const SearchArgs A) {
   using G = Geom<PS, SG>;
@@ -619,6 +658,8 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
     }
     typename std::conditional<kPacked, Window8P, Window8<SG>>::type Wn;
     Wn.bx = -1; Wn.by = -1;
+    TapWindow<PS, kUseTapWindow<PS, SG> ? SG : 32> Wt;       // (SG 32: a one-element dummy for the sizes that do not use it)
+    Wt.bx = -1; Wt.by = -1;
     Template8P Tp;
     if constexpr (kPacked && !kTsmem) Tp.set(T);
     if constexpr (kTsmem) {
@@ -652,6 +693,11 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
         if constexpr (kTsmem) sg = sample_window8p(Wn, px, py, A.patnorm, Template8S{&tsm[threadIdx.x >> 5][0][lane]}, A.one);
         else if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Template8R{&Tp}, A.one);
         else sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
+      } else if constexpr (kUseTapWindow<PS, SG>) {
+        const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
+        DIS_CHECK(A, gather_in_plane<PS>(A, tb.y * tw + tb.x), 104);
+        if (__any_sync(kFull, active && (tb.x != Wt.bx || tb.y != Wt.by))) Wt.load(imB, tw, eoff, tb.x, tb.y);
+        sg = sample_tapwindow<PS, SG>(Wt, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
       }
@@ -983,8 +1029,9 @@ constexpr float kEarlyStep = 0.3f;   // px; measured on the bench workload: 0.1 
 constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
 constexpr int kStragWarps = 4;
 constexpr long long kYieldGraceCycles = 20000;   // ~10 us: the walk's blocks announce themselves within a few us of their launch
+__host__ __device__ constexpr int strag_min_blocks(int ps) { return (ps == 10 || ps == 12) ? DIS_BIG_BLOCKS : 1; }
 template <int PS, int SG, bool FAST>
-__global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArgs A) {
+__global__ void __launch_bounds__(kStragWarps * 32, strag_min_blocks(PS)) k_stragglers(const SearchArgs A) {
   using G = Geom<PS, SG>;
   extern __shared__ float tiles[];
   const int th = A.height + 2 * A.pad;
@@ -1088,6 +1135,8 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
     Wn.bx = -1; Wn.by = -1;
     Template8P Tp;
     if constexpr (kPacked) Tp.set(T);
+    TapWindow<PS, kUseTapWindow<PS, SG> ? SG : 32> Wt;
+    Wt.bx = -1; Wt.by = -1;
     int ox = 0, oy = 0;
     if (PS == 8 && use_tile) {
       const int2 tb0 = tap_base<PS>(stx, sty, A.pad, wmax, hmax);
@@ -1116,6 +1165,10 @@ __global__ void __launch_bounds__(kStragWarps * 32) k_stragglers(const SearchArg
         }
         if constexpr (kPacked) sg = sample_window8p(Wn, px, py, A.patnorm, Template8R{&Tp}, A.one);
         else sg = sample_window8<SG>(Wn, px, py, A.patnorm, T);
+      } else if constexpr (kUseTapWindow<PS, SG>) {
+        const int2 tb = tap_base<PS>(px, py, A.pad, wmax, hmax);
+        if (__any_sync(kFull, active && (tb.x != Wt.bx || tb.y != Wt.by))) Wt.load(imB, tw, eoff, tb.x, tb.y);
+        sg = sample_tapwindow<PS, SG>(Wt, px, py, A.patnorm, T);
       } else {
         sg = sample_and_project<PS, SG>(imB, tw, A.pad, wmax, hmax, px, py, sl, A.patnorm, eoff, T);
       }

@@ -96,3 +96,31 @@ def test_product_never_touches_the_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
                 assert "oracle" not in open(os.path.join(dp, f), errors="ignore").read().lower(), f
+
+
+def test_packed_arithmetic_is_not_contracted():
+    """ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into one FFMA2 (it honours the rounding modifiers and
+    --fmad=false only for scalar code), which would break bit parity.  csrc/dis_search.cu therefore writes every packed
+    addition as fma(a, ONE, b) with a run-time ONE.  Check the SASS of the build: a sample of k_converge<8,4> must be
+    exactly 48 packed multiplications (4 x 8 bilinear + 2 x 8 projections) and 53 packed additions (3 x 8 bilinear,
+    8 mean subtractions, 3 x 7 tree sums) — a contracted pair would show up as one FFMA2 less and one FMUL2 less."""
+    import shutil
+    import subprocess
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not available")
+    lib = os.path.join(ROOT, "optical-flow-using-dense-inverse-search_b200", "libdis_b200.so")
+    names = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
+    fn, body = None, []
+    for line in names.splitlines():
+        if "Function :" in line:
+            fn = line.split("Function :")[1].strip()
+        elif fn and "k_convergeILi8ELi4ELb0" in fn:
+            body.append(line)
+    assert body, "k_converge<8, 4, false> not found in the library"
+    text = "\n".join(body)
+    n_mul = sum(1 for l in body if " FMUL2 " in l)
+    n_fma = sum(1 for l in body if " FFMA2 " in l)
+    # (the compiler keeps an out-of-line copy of one 7-addition tree sum for a warp that reaches the shuffles diverged:
+    #  60 FFMA2 in all; a contracted pair would remove one FMUL2)
+    assert n_mul == 48 and n_fma >= 53, f"packed arithmetic contracted or restructured: FMUL2 {n_mul}, FFMA2 {n_fma}"
+    assert " FADD2 " not in text            # every packed addition goes through the opaque-one FFMA2
