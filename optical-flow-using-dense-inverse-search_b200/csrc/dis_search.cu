@@ -46,7 +46,14 @@ namespace {
 
 constexpr int kSlots = kWalkSeeds;    // cache entries per patch: 4 sets (bit 0 of x, bit 0 of y) x kSlots/4 ways
 static_assert(kSlots == 16 || kSlots == 32, "cache geometry");
-constexpr int kWays = kSlots / 4;
+// Ways per set.  4: 4 sets x 4 ways, the predicted way is probed in the fast loop and the other three once per chunk.
+// 1 (-DDIS_WAYS=1, direct-mapped): no second probe and a one-store insertion, but two hot positions of a patch that share a
+// slot evict each other on every visit: 41.2 instead of 32.4 sampled passes per patch and 35.9 instead of 31.4 ms per
+// bench step (profiles/r2_direct_mapped_ab.log; tools/trace predicted it once hand-offs were counted).  Kept as an experiment.
+#ifndef DIS_WAYS
+#define DIS_WAYS 4
+#endif
+constexpr int kWays = DIS_WAYS == 1 ? 1 : kSlots / 4;
 constexpr int kWayBits = kSlots == 32 ? 3 : 2;
 // Slot predicted for a position.  16 slots: (5x + y) mod 16 — the best of the lattice hashes (ax + by) mod 16 on the
 // position traces of the bench workload: half as many hits in a non-predicted way as "low 2 bits of x above low 2 bits of y" (the orbit of a
@@ -504,6 +511,14 @@ __device__ __forceinline__ bool gather_in_plane(const SearchArgs& A, int c) {
 template <int STRIDE, bool DEDUP>
 __device__ __forceinline__ bool cache_insert(uint4* cache, unsigned& fifo, const uint4 e) {
   const int p = slot_of(e.x, e.y);
+  if (kWays == 1) {                                             // direct-mapped: the newest position owns the slot
+    if (DEDUP) {
+      const uint2 old = *reinterpret_cast<const uint2*>(cache + p * STRIDE);
+      if (old.x == e.x && old.y == e.y) return true;
+    }
+    cache[p * STRIDE] = e;
+    return false;
+  }
   const uint4 old = cache[p * STRIDE];
   if (DEDUP) {
     if (old.x == e.x && old.y == e.y) return true;
@@ -860,7 +875,8 @@ k_inverse_search(const SearchArgs A) {
     int chunk = 0;
 #pragma unroll 1
     do {
-      run = run && k + kChunk <= iters + 1;
+      const bool budget = k + kChunk <= iters + 1;            // enough passes left for a whole chunk
+      run = run && budget;
 #pragma unroll
       for (int it = 0; it < kChunk; ++it) {
         if (DIS_EARLY && it == DIS_EARLY && !__any_sync(kFull, run)) break;
@@ -875,7 +891,12 @@ k_inverse_search(const SearchArgs A) {
           if (FAST) { if (dx * dx + dy * dy < A.conv_eps2) { run = false; fin = true; } }
         }
       }
-      const bool probe = state == ST_RUN && !run && !fin && !missed;
+      bool probe = state == ST_RUN && !run && !fin && !missed;
+      if (kWays == 1) {
+        // direct-mapped: a lane that fell out of a chunk it had entered met a first-seen position; only a lane near the
+        // end of its budget still has to step, one pass per chunk, through the slot test below
+        if (probe && budget) { missed = true; probe = false; }
+      }
       if (__any_sync(kFull, probe)) {
         if (probe) {
           const unsigned bx = __float_as_uint(px), by = __float_as_uint(py);

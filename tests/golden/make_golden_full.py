@@ -31,7 +31,10 @@ CASES = [
     dict(name="sintel_seed1", src=("pair", 1024, 436, 1, None), params={}),
     dict(name="sintel_seed2", src=("pair", 1024, 436, 2, None), params={}),
     dict(name="sintel_amp14", src=("pair", 1024, 436, 3, 14.0), params={}),                 # large motion: many resets
-    dict(name="sintel_lowtex", src=("lowtex", 1024, 436, 4), params={}),                    # half the frame flat
+    # half the frame flat: the compiled REFERENCE crashes on this input (a solve yields NaN and src/patch.cpp:222-234 then
+    # indexes out of bounds), so this one golden comes from the C restatement, whose convention
+    # (NaN => reset to the initial u) the engine shares; "oracle": "port" marks it
+    dict(name="sintel_lowtex", src=("lowtex", 1024, 436, 4), params={}, oracle="port"),
     dict(name="bench_seq100_pair0", src=("seq", 50, 1024, 436, 100, 0), params={}),        # the timed workload of bench.py
     dict(name="bench_seq100_pair24", src=("seq", 50, 1024, 436, 100, 24), params={}),
     dict(name="bench_seq100_pair48", src=("seq", 50, 1024, 436, 100, 48), params={}),
@@ -64,12 +67,12 @@ def make_input(src):
 def run_case(c):
     import oracle
     t0 = time.time()
-    ref = oracle.Oracle("reference")
+    ref = oracle.Oracle(c.get("oracle", "reference"))
     a, b, gt = make_input(tuple(c["src"]))
     flow, d = ref.run_pair_u8(a, b, dump=True, **c["params"])
     w = a.shape[1]
     sub = 16 if w >= 3000 else 8 if w >= 1024 else 4
-    m = dict(name=c["name"], src=list(c["src"]), params=c["params"], w=int(a.shape[1]), h=int(a.shape[0]),
+    m = dict(name=c["name"], src=list(c["src"]), params=c["params"], oracle=c.get("oracle", "reference"), w=int(a.shape[1]), h=int(a.shape[0]),
              frames_sha=sha(np.stack([a, b])), flow_sha=sha(flow), level_flow_sha=[sha(f) for f in d["flow"]],
              level_ref_sha=[sha(r) for r in d["ref"]], level_info=d["info"], sub=sub,
              epe_vs_gt=float(np.linalg.norm(flow - gt, axis=-1).mean()), seconds=time.time() - t0)
