@@ -74,6 +74,9 @@ __host__ __device__ constexpr int way_xor(int w) { return ((w & 1) << 1) | ((w >
 #ifndef DIS_PACKED
 #define DIS_PACKED 1      // packed fp32x2 arithmetic in the sampling code of k_converge / k_stragglers (ps 8)
 #endif
+#ifndef DIS_MOVED_ROLLING
+#define DIS_MOVED_ROLLING 1   // the early hand-off rule of k_converge looks at the last three executed passes (0: only passes 21-23, round 1)
+#endif
 #ifndef DIS_CHUNK
 #define DIS_CHUNK 6
 #endif
@@ -686,7 +689,7 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
     }
     int k = 0;
     unsigned ns = 0, fifo = 0;
-    float moved = 0.f;                                        // largest |delta u| component of the last three passes
+    float mv0 = 0.f, mv1 = 0.f, mv2 = 0.f;                    // |delta u| (largest component) of the last three EXECUTED passes
     __syncwarp();
 #pragma unroll
     for (int i = lane; i < G::G * kSlots; i += 32) img_warp[i] = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
@@ -721,7 +724,11 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
         if (sl == 0 && pass >= kN1 - kSeed)
           if (cache_insert<1, true>(img, fifo, make_uint4(__float_as_uint(px), __float_as_uint(py), __float_as_uint(d.x), __float_as_uint(d.y))))
             fifo |= 0x80000000u;                                // "settled" rides in the unused top bit
-        if (pass >= kN1 - 3) moved = fmaxf(moved, fmaxf(fabsf(d.x), fabsf(d.y)));
+#if DIS_MOVED_ROLLING
+        mv2 = mv1; mv1 = mv0; mv0 = fmaxf(fabsf(d.x), fabsf(d.y));   // a batch may leave at any pass from conv_min on
+#else
+        if (pass >= kN1 - 3) mv0 = fmaxf(mv0, fmaxf(fabsf(d.x), fabsf(d.y)));
+#endif
         ++k; ++ns;
         ux = ux - d.x; uy = uy - d.y;                         // src/patch.cpp:179
         px = refx + ux; py = refy + uy;                       // src/patch.cpp:182
@@ -731,6 +738,7 @@ __global__ void __launch_bounds__(conv_warps(PS) * 32, conv_blocks(PS)) k_conver
     // A patch that still moves by a sizeable step after kN1 passes almost never settles (its walk would miss on
     // most passes): it goes to k_stragglers right away instead of after handoff_misses expensive walk misses.
     bool handed = false;
+    const float moved = fmaxf(mv0, fmaxf(mv1, mv2));
     if (have && active && sl == 0 && A.stragglers && A.early_step > 0.f && moved >= A.early_step) {
       const int slot = atomicAdd(A.straggler_count, 1);
       if (slot < A.straggler_cap) {
