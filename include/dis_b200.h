@@ -273,6 +273,21 @@ DIS_API int dis_color_code(dis_engine* e, const float* flow, int w, int h, float
  * with dis_color_code (tools/dis_sequence.cpp does). */
 DIS_API int dis_color_code_pair(dis_engine* e, int pair, float maxmotion, uint8_t* bgr_out);
 
+/* ---- colour coding without any allocation ------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic and
+ * byte-identical output as dis_color_code, but d_flow (h x w x 2 fp32) and d_bgr_out (h x w x 3 u8) are the CALLER's
+ * DEVICE buffers on CUDA device `device`, the work is enqueued on `cuda_stream` (a cudaStream_t; NULL = the default
+ * stream) and the call returns without synchronising.  It needs no engine handle and calls no cudaMalloc / cudaFree /
+ * allocating routine: the scratch of the max-|u| reduction is a fixed 33 KB __device__ array inside the library (one
+ * per GPU that loads it, held until exit).  Limit: w * h <= DIS_NOALLOC_MAX_PIXELS (33 554 432, e.g. 7680 x 4320);
+ * larger fields are rejected with DIS_ERR_PARAM (use dis_color_code).  Every call on a GPU shares that one array:
+ * calls that overlap on the GPU (different streams or threads) race; calls ordered on one stream do not. */
+#define DIS_NOALLOC_PIXELS_PER_PARTIAL 4096
+#define DIS_NOALLOC_MAX_PIXELS (8192 * DIS_NOALLOC_PIXELS_PER_PARTIAL)
+DIS_API int dis_color_code_device_noalloc(int device, const float* d_flow, int w, int h, float maxmotion,
+                                          uint8_t* d_bgr_out, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -66,6 +66,9 @@ struct Level {            // one entry per scale finest..coarsest, index s = sca
 
 }  // namespace
 
+// the error slot of dis_last_error() for the other translation units of the library (dis_noalloc.cu)
+namespace dis { int set_last_error(int code, const char* msg) { return fail(code, msg ? msg : ""); } }
+
 struct dis_engine {
   dis_params prm;
   int device = 0;

@@ -148,6 +148,7 @@ int launch_upsample_crop(const float* dense, size_t dense_stride, int Wf, int Hf
                          int top, float* out, int w, int h, int n_pairs, cudaStream_t s);
 
 // Middlebury colour coding (src/color_coding.cpp): flow [n_pixels][2] -> bgr [n_pixels][3]; scratch: one unsigned
+int set_last_error(int code, const char* msg);   // dis_api.cu: records msg for dis_last_error(), returns code
 int launch_color_code(const float* flow, size_t n_pixels, float maxmotion, unsigned* scratch, uint8_t* bgr, cudaStream_t s);
 
 }  // namespace dis

@@ -57,6 +57,7 @@ ABI_SYMBOLS = [
     "dis_pool_run_batch_u8", "dis_pool_run_sequence_u8", "dis_pool_get_stats", "dis_pool_last_ms", "dis_pool_host_alloc",
     "dis_pool_host_free", "dis_pool_run_pair_tiled_u8", "dis_tiled_fetch_u_rows", "dis_tiled_densify_rows",
     "dis_tiled_finish_rows", "dis_tiled_end", "dis_tiled_last_ms", "dis_pool_last_tiled_device_ms",
+    "dis_color_code_device_noalloc",
 ]
 
 
@@ -400,6 +401,19 @@ class Pool:
 
     def host_free(self, ptr: int) -> None:
         self._chk(self.lib.dis_pool_host_free(self._h, C.c_void_p(ptr)))
+
+
+NOALLOC_MAX_PIXELS = 8192 * 4096   # DIS_NOALLOC_MAX_PIXELS of include/dis_b200.h
+
+
+def color_code_device_noalloc(device: int, d_flow_ptr: int, w: int, h: int, d_bgr_ptr: int, maxmotion: float = -1.0,
+                              stream: int = 0) -> None:
+    """dis_color_code_device_noalloc: colour coding of a DEVICE flow field into a DEVICE image, enqueued on `stream`, with
+    no allocation of any kind (fixed scratch inside the library; w*h <= NOALLOC_MAX_PIXELS).  No counterpart in the
+    reference; same bytes as Engine.color_code.  Calls overlapping on one GPU race on the shared scratch."""
+    lib = load_library()
+    _chk(lib.dis_color_code_device_noalloc(C.c_int(device), C.c_void_p(d_flow_ptr), C.c_int(w), C.c_int(h), C.c_float(maxmotion),
+                                           C.c_void_p(d_bgr_ptr), C.c_void_p(stream)))
 
 
 def write_flo(path: str, flow: np.ndarray) -> None:
