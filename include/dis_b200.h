@@ -113,6 +113,12 @@ DIS_API int dis_run_batch_u8(dis_engine* e, const uint8_t* const* a, const uint8
 DIS_API int dis_run_sequence_u8(dis_engine* e, const uint8_t* frames, int n_frames, int w, int h,
                                 int stride, size_t frame_stride, float* flow_out);
 
+/* Host-buffer calls of 8 pairs or more return the flows in slices (the finest level is searched in two parts and the first
+ * part's flows travel home during the second).  enabled = 0 turns that off for this engine: worth it when something else
+ * hides the copies, e.g. a second engine on the same GPU (dis_pool_submit_*).  Results do not change.  No counterpart in
+ * the reference. */
+DIS_API int dis_set_host_slices(dis_engine* e, int enabled);
+
 /* ---- the exact OpticalFlowClass contract ---------------------------------------------------
  * Replaces OpticalFlow::OpticalFlowClass::OpticalFlowClass (include/optical_flow.hpp:43-54,
  * src/optical_flow.cpp:19-132) with draw_grid = false.  Six HOST pyramids indexed by absolute
@@ -247,6 +253,19 @@ DIS_API int dis_pool_run_batch_u8(dis_pool* pool, const uint8_t* const* a, const
                                   int h, int stride, float* flow_out);                       /* BASELINE config 3 */
 DIS_API int dis_pool_run_sequence_u8(dis_pool* pool, const uint8_t* frames, int n_frames, int w, int h, int stride,
                                      size_t frame_stride, float* flow_out);                  /* BASELINE config 2 over N GPUs */
+/* Asynchronous form of the two calls above (the reference's loop, src/main.cpp:102, has no counterpart: it is sequential).
+ * A submission is ONE whole dis_run_sequence_u8 / dis_run_batch_u8 on ONE engine of the pool — the idle one, else the one
+ * with the shortest queue — and returns a ticket at once; the caller's buffers belong to the pool until dis_pool_wait
+ * returns for that ticket (its status is the call's; stats / worker may be NULL).  List a GPU TWICE in dis_pool_create and
+ * keep two submissions in flight: the uploads and downloads of one run under the kernels of the other (bench.py's `e2e`).
+ * Results are bit-identical to the blocking calls.  Tickets are waited for in any order, each once; dis_pool_wait_all
+ * drains every outstanding ticket and returns the first failure.  One host thread submits and waits. */
+DIS_API int dis_pool_submit_sequence_u8(dis_pool* pool, const uint8_t* frames, int n_frames, int w, int h, int stride,
+                                        size_t frame_stride, float* flow_out, int* ticket);
+DIS_API int dis_pool_submit_batch_u8(dis_pool* pool, const uint8_t* const* a, const uint8_t* const* b, int n_pairs, int w,
+                                     int h, int stride, float* flow_out, int* ticket);
+DIS_API int dis_pool_wait(dis_pool* pool, int ticket, dis_stats* stats, int* worker);
+DIS_API int dis_pool_wait_all(dis_pool* pool);
 /* ONE large pair split over the pool's GPUs by bands of grid rows with a per-level halo exchange over NVLink peer
  * memory (BASELINE config 5).  Every GPU gets both frames and builds the pyramids redundantly (< 1 % of
  * the work); per level it searches only the patches of its band, pulls the ceil(ps / (2 steps)) + 1 boundary grid rows

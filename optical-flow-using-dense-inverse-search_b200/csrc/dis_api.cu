@@ -103,6 +103,7 @@ struct dis_engine {
   bool stats_fetched = false;
   bool out_sent = false;                // the last run already copied its flows to the caller's buffer
   bool keep_iters = true;
+  bool host_slices = true;              // dis_set_host_slices
   int max_groups = 1;                   // DIS_GROUPS overrides; measured: no gain on B200 (levels are work-bound, not tail-bound)
 
   DevBuf frames_u8, frames_f32, pairs, planes_all, out, counters, stragglers, stage, walk;
@@ -362,6 +363,7 @@ int run_levels(dis_engine* e, float* host_out = nullptr) {
   e->n_groups = G;
   e->search_launches = nl;
   if (host_out && (G > 1 || e->n_pairs < 8 || (dis::tuning().out_slices_nw == 0 && dis::tuning().out_slices_n >= 0 && dis::tuning().out_slices_n <= 1))) host_out = nullptr;
+  if (!e->host_slices) host_out = nullptr;
   if (host_out && !e->copy_stream) CU(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
   if (host_out && e->out.ensure(sizeof(float) * 2 * (size_t)e->w0 * e->h0 * e->n_pairs)) return fail(DIS_ERR_ALLOC, "cudaMalloc(out) failed");
   e->out_sent = host_out != nullptr;
@@ -526,6 +528,12 @@ void dis_destroy(dis_engine* e) {
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
+}
+
+int dis_set_host_slices(dis_engine* e, int enabled) {
+  if (!e) return fail(DIS_ERR_PARAM, "null engine");
+  e->host_slices = enabled != 0;
+  return DIS_OK;
 }
 
 int dis_upload_frames_u8(dis_engine* e, const uint8_t* frames, int n_frames, int w, int h, int stride,

@@ -15,7 +15,9 @@
 
 #include <chrono>
 #include <condition_variable>
+#include <deque>
 #include <functional>
+#include <map>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -60,8 +62,11 @@ struct Worker {
   std::thread th;
   std::mutex m;
   std::condition_variable cv;
-  std::function<int(dis_engine*)> job;
-  bool has_job = false, done = false, quit = false;
+  struct Task { std::function<int(dis_engine*)> fn; int ticket; };   // ticket < 0: a blocking call waits on `done`
+  std::deque<Task> q;
+  int backlog = 0;      // queued + running tasks (under m)
+  dis_pool* pool = nullptr;
+  bool done = false, quit = false;
   int rc = DIS_OK;
   std::string err;
   double ms = 0;       // wall time of the last job on this worker
@@ -75,6 +80,12 @@ struct dis_pool {
   dis_params prm;
   double wall_ms = 0;
   bool peers_ready = false;
+  // asynchronous submissions (dis_pool_submit_*): one record per ticket until it is waited for
+  struct Ticket { bool done = false; int rc = DIS_OK; std::string err; int worker = -1; dis_stats stats; double ms = 0; };
+  std::mutex tm;
+  std::condition_variable tcv;
+  std::map<int, Ticket> tickets;
+  int next_ticket = 1, last_worker = -1;
 };
 
 namespace {
@@ -99,19 +110,34 @@ void worker_main(Worker* w, const dis_params* prm, bool bind) {
   w->cv.notify_all();
   if (rc) return;
   for (;;) {
-    std::function<int(dis_engine*)> job;
+    Worker::Task task;
     {
       std::unique_lock<std::mutex> g(w->m);
-      w->cv.wait(g, [&] { return w->has_job || w->quit; });
-      if (w->quit) break;
-      job = std::move(w->job);
-      w->has_job = false;
+      w->cv.wait(g, [&] { return !w->q.empty() || w->quit; });
+      if (w->q.empty()) break;          // quit: only once the queue has drained
+      task = std::move(w->q.front());
+      w->q.pop_front();
     }
     const auto t0 = std::chrono::steady_clock::now();
-    rc = job(w->eng);
+    rc = task.fn(w->eng);
     const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (task.ticket >= 0) {             // asynchronous submission: the result goes to the ticket
+      dis_stats st;
+      memset(&st, 0, sizeof st);
+      const std::string err = rc ? dis_last_error() : "";
+      if (!rc) dis_get_stats(w->eng, &st);
+      { std::lock_guard<std::mutex> g(w->m); --w->backlog; }
+      {
+        std::lock_guard<std::mutex> g(w->pool->tm);
+        dis_pool::Ticket& t = w->pool->tickets[task.ticket];
+        t.done = true; t.rc = rc; t.err = err; t.stats = st; t.ms = ms;
+      }
+      w->pool->tcv.notify_all();
+      continue;
+    }
     {
       std::lock_guard<std::mutex> g(w->m);
+      --w->backlog;
       w->rc = rc;
       w->err = rc ? dis_last_error() : "";
       w->ms = ms;
@@ -123,14 +149,37 @@ void worker_main(Worker* w, const dis_params* prm, bool bind) {
   w->eng = nullptr;
 }
 
-void submit(Worker* w, std::function<int(dis_engine*)> job) {
+void submit(Worker* w, std::function<int(dis_engine*)> job, int ticket = -1) {
   {
     std::lock_guard<std::mutex> g(w->m);
-    w->job = std::move(job);
-    w->has_job = true;
-    w->done = false;
+    w->q.push_back(Worker::Task{std::move(job), ticket});
+    ++w->backlog;
+    if (ticket < 0) w->done = false;
   }
   w->cv.notify_all();
+}
+
+// asynchronous submission: the whole call goes to the worker with the shortest queue (ties: the one after the last
+// used), so equal jobs alternate between the engines
+int submit_ticket(dis_pool* p, std::function<int(dis_engine*)> job, int* ticket) {
+  const int R = (int)p->w.size();
+  int best = -1, best_n = 0;
+  for (int k = 1; k <= R; ++k) {
+    const int i = (p->last_worker + k) % R;
+    int n;
+    { std::lock_guard<std::mutex> g(p->w[i]->m); n = p->w[i]->backlog; }
+    if (best < 0 || n < best_n) { best = i; best_n = n; }
+  }
+  p->last_worker = best;
+  int t;
+  {
+    std::lock_guard<std::mutex> g(p->tm);
+    t = p->next_ticket++;
+    p->tickets[t].worker = best;
+  }
+  submit(p->w[best], std::move(job), t);
+  *ticket = t;
+  return DIS_OK;
 }
 
 int wait_done(Worker* w) {
@@ -185,6 +234,7 @@ int dis_pool_create(const dis_params* p, const int* devices, int n_devices, dis_
   for (int i = 0; i < n_devices; ++i) {
     Worker* w = new Worker();
     w->device = devices ? devices[i] : i;
+    w->pool = pool;
     pool->w.push_back(w);
     w->th = std::thread(worker_main, w, &pool->prm, bind);
   }
@@ -195,6 +245,11 @@ int dis_pool_create(const dis_params* p, const int* devices, int n_devices, dis_
     if (r && !rc) { rc = r; err = "GPU " + std::to_string(w->device) + ": " + w->err; }
   }
   if (rc) { dis_pool_destroy(pool); return pfail(rc, err); }
+  for (Worker* w : pool->w) {   // engines that share a GPU hide each other's copies: no output slices (each costs a launch tail)
+    int same = 0;
+    for (Worker* v : pool->w) same += v->device == w->device;
+    if (same > 1) dis_set_host_slices(w->eng, 0);
+  }
   *out = pool;
   return DIS_OK;
 }
@@ -255,6 +310,54 @@ int dis_pool_run_sequence_u8(dis_pool* p, const uint8_t* frames, int n_frames, i
       };
   }
   return run_all(p, jobs);
+}
+
+// ---- asynchronous form: whole calls queued to the engines ---------------------------------------------------------
+// A submission is ONE dis_run_sequence_u8 / dis_run_batch_u8 on ONE engine (not sharded): the pool hands it to the
+// worker with the shortest queue and returns a ticket at once.  With a GPU listed twice in dis_pool_create, two
+// consecutive submissions run on two engines of that GPU: the uploads and downloads of one overlap with the kernels of
+// the other, and the latency-bound level tails of one are filled by the other's blocks.
+int dis_pool_submit_sequence_u8(dis_pool* p, const uint8_t* frames, int n_frames, int w, int h, int stride,
+                                size_t frame_stride, float* flow_out, int* ticket) {
+  if (!p || !frames || !flow_out || !ticket) return pfail(DIS_ERR_PARAM, "null argument");
+  if (n_frames < 2 || w <= 0 || h <= 0 || stride < w || frame_stride < (size_t)stride * h)
+    return pfail(DIS_ERR_PARAM, "bad sequence geometry");
+  return submit_ticket(p, [=](dis_engine* e) { return dis_run_sequence_u8(e, frames, n_frames, w, h, stride, frame_stride, flow_out); }, ticket);
+}
+
+int dis_pool_submit_batch_u8(dis_pool* p, const uint8_t* const* a, const uint8_t* const* b, int n_pairs, int w, int h,
+                             int stride, float* flow_out, int* ticket) {
+  if (!p || !a || !b || !flow_out || !ticket) return pfail(DIS_ERR_PARAM, "null argument");
+  if (n_pairs <= 0 || w <= 0 || h <= 0 || stride < w) return pfail(DIS_ERR_PARAM, "bad batch geometry");
+  std::vector<const uint8_t*> pa(a, a + n_pairs), pb(b, b + n_pairs);   // the pointer arrays may be temporaries of the caller
+  return submit_ticket(p, [=](dis_engine* e) { return dis_run_batch_u8(e, pa.data(), pb.data(), n_pairs, w, h, stride, flow_out); }, ticket);
+}
+
+int dis_pool_wait(dis_pool* p, int ticket, dis_stats* stats, int* worker) {
+  if (!p) return pfail(DIS_ERR_PARAM, "null pool");
+  std::unique_lock<std::mutex> g(p->tm);
+  auto it = p->tickets.find(ticket);
+  if (it == p->tickets.end()) return pfail(DIS_ERR_STATE, "unknown ticket (never issued, or already waited for)");
+  p->tcv.wait(g, [&] { return it->second.done; });
+  const dis_pool::Ticket t = it->second;
+  p->tickets.erase(it);
+  g.unlock();
+  if (stats) *stats = t.stats;
+  if (worker) *worker = t.worker;
+  return t.rc ? pfail(t.rc, "GPU " + std::to_string(p->w[t.worker]->device) + ": " + t.err) : DIS_OK;
+}
+
+int dis_pool_wait_all(dis_pool* p) {
+  if (!p) return pfail(DIS_ERR_PARAM, "null pool");
+  int rc = DIS_OK;
+  std::string err;
+  for (;;) {
+    int t;
+    { std::lock_guard<std::mutex> g(p->tm); if (p->tickets.empty()) break; t = p->tickets.begin()->first; }
+    const int r = dis_pool_wait(p, t, nullptr, nullptr);
+    if (r && !rc) { rc = r; err = g_pool_err; }
+  }
+  return rc ? pfail(rc, err) : DIS_OK;
 }
 
 // ---- one large pair over the pool's GPUs: bands of grid rows + halo exchange -----------------------

@@ -57,7 +57,8 @@ ABI_SYMBOLS = [
     "dis_pool_run_batch_u8", "dis_pool_run_sequence_u8", "dis_pool_get_stats", "dis_pool_last_ms", "dis_pool_host_alloc",
     "dis_pool_host_free", "dis_pool_run_pair_tiled_u8", "dis_tiled_fetch_u_rows", "dis_tiled_densify_rows",
     "dis_tiled_finish_rows", "dis_tiled_end", "dis_tiled_last_ms", "dis_pool_last_tiled_device_ms",
-    "dis_color_code_device_noalloc",
+    "dis_color_code_device_noalloc", "dis_set_host_slices", "dis_pool_submit_sequence_u8", "dis_pool_submit_batch_u8",
+    "dis_pool_wait", "dis_pool_wait_all",
 ]
 
 
@@ -167,6 +168,10 @@ class Engine:
         out = np.empty((h, w, 3), np.uint8)
         _chk(self.lib.dis_color_code_pair(self._h, pair, C.c_float(maxmotion), out.ctypes.data_as(_u8p)))
         return out
+
+    def set_host_slices(self, enabled: bool) -> None:
+        """dis_set_host_slices: host-buffer calls return the flows in slices (default) or in one copy at the end."""
+        _chk(self.lib.dis_set_host_slices(self._h, C.c_int(1 if enabled else 0)))
 
     def run_batch(self, a: np.ndarray, b: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
         a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
@@ -349,6 +354,42 @@ class Pool:
         pb = (C.c_void_p * n)(*[b.ctypes.data + i * h * w for i in range(n)])
         self._chk(self.lib.dis_pool_run_batch_u8(self._h, pa, pb, n, w, h, w, out.ctypes.data_as(_fp)))
         return out
+
+    # -- asynchronous form: a whole call per engine, tickets (dis_pool_submit_* / dis_pool_wait) --
+    def submit_sequence_ptr(self, frames_ptr: int, n: int, w: int, h: int, out_ptr: int) -> int:
+        """Queue one whole sequence call on the idlest engine; the buffers belong to the pool until wait(ticket)."""
+        t = C.c_int(0)
+        self._chk(self.lib.dis_pool_submit_sequence_u8(self._h, C.cast(C.c_void_p(frames_ptr), _u8p), n, w, h, w, C.c_size_t(h * w),
+                                                       C.cast(C.c_void_p(out_ptr), _fp), C.byref(t)))
+        return t.value
+
+    def submit_sequence(self, frames: np.ndarray, out: np.ndarray) -> int:
+        assert frames.dtype == np.uint8 and frames.flags.c_contiguous and out.dtype == np.float32 and out.flags.c_contiguous
+        n, h, w = frames.shape
+        assert out.shape == (n - 1, h, w, 2)
+        return self.submit_sequence_ptr(frames.ctypes.data, n, w, h, out.ctypes.data)
+
+    def submit_batch(self, a: np.ndarray, b: np.ndarray, out: np.ndarray) -> int:
+        assert a.dtype == np.uint8 and a.flags.c_contiguous and b.dtype == np.uint8 and b.flags.c_contiguous
+        n, h, w = a.shape
+        assert out.dtype == np.float32 and out.flags.c_contiguous and out.shape == (n, h, w, 2)
+        pa = (C.c_void_p * n)(*[a.ctypes.data + i * h * w for i in range(n)])
+        pb = (C.c_void_p * n)(*[b.ctypes.data + i * h * w for i in range(n)])
+        t = C.c_int(0)
+        self._chk(self.lib.dis_pool_submit_batch_u8(self._h, pa, pb, n, w, h, w, out.ctypes.data_as(_fp), C.byref(t)))
+        return t.value
+
+    def wait(self, ticket: int) -> dict:
+        """Wait for one submission; returns its stats plus the worker that ran it."""
+        st = DisStats()
+        wk = C.c_int(-1)
+        self._chk(self.lib.dis_pool_wait(self._h, C.c_int(ticket), C.byref(st), C.byref(wk)))
+        d = {k: int(getattr(st, k)) for k, _ in DisStats._fields_}
+        d["worker"] = wk.value
+        return d
+
+    def wait_all(self) -> None:
+        self._chk(self.lib.dis_pool_wait_all(self._h))
 
     def run_pair_tiled(self, a: np.ndarray, b: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
         """One large pair over all the pool's GPUs: bands of grid rows + per-level halo exchange over peer memory."""

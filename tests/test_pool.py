@@ -90,3 +90,64 @@ def test_pool_pinned_buffers_and_errors(seq):
         p.close()
     with pytest.raises(dis_b200.DisError):
         dis_b200.Pool([99])
+
+
+@pytest.mark.gpu
+def test_pool_async_submissions_equal_blocking_calls(seq):
+    """dis_pool_submit_* / dis_pool_wait: whole calls queued to the engines (two engines on one GPU hide each other's
+    copies); flows, stats and errors are those of the blocking call, in any waiting order."""
+    frames, ref, st = seq
+    n, h, w = frames.shape
+    for devs in devices_for_test():
+        p = dis_b200.Pool(devs)
+        try:
+            outs = [np.zeros_like(ref) for _ in range(5)]
+            tickets = [p.submit_sequence(frames, o) for o in outs[:4]]
+            tickets.append(p.submit_batch(frames[:-1], frames[1:], outs[4]))
+            assert len(set(tickets)) == 5
+            workers = []
+            for t, o in reversed(list(zip(tickets, outs))):            # waited for in reverse order
+                s = p.wait(t)
+                assert np.array_equal(bits(o), bits(ref)), f"ticket {t} over devices {devs}"
+                assert s["patches"] == st["patches"] and s["patch_iterations"] == st["patch_iterations"]
+                workers.append(s["worker"])
+            assert len(set(workers)) == min(len(devs), 5)              # equal jobs spread over all the engines
+            with pytest.raises(dis_b200.DisError):
+                p.wait(tickets[0])                                     # a ticket is waited for once
+            with pytest.raises(dis_b200.DisError):
+                p.wait(12345)
+            with pytest.raises(dis_b200.DisError):
+                p.submit_sequence(frames[:1], np.zeros((0, h, w, 2), np.float32))
+            # a failing job reports through its ticket, the pool stays usable; blocking calls queue behind submissions
+            big = dis_b200.Pool(devs, coarsest_scale=9)
+            try:
+                small = np.zeros((2, 64, 64), np.uint8)
+                t = big.submit_sequence(small, np.zeros((1, 64, 64, 2), np.float32))
+                with pytest.raises(dis_b200.DisError):
+                    big.wait(t)
+            finally:
+                big.close()
+            t1 = p.submit_sequence(frames, outs[0])
+            again = p.run_sequence(frames)
+            assert np.array_equal(bits(again), bits(ref))
+            t2 = p.submit_sequence(frames, outs[1])
+            p.wait_all()
+            assert np.array_equal(bits(outs[0]), bits(ref)) and np.array_equal(bits(outs[1]), bits(ref))
+            with pytest.raises(dis_b200.DisError):
+                p.wait(t2)
+            del t1
+        finally:
+            p.close()
+
+
+@pytest.mark.gpu
+def test_host_slices_switch_does_not_change_results():
+    frames, _ = dis_b200.synth.make_sequence(10, 200, 100, seed=5)
+    e = dis_b200.Engine(0)
+    a = e.run_sequence(frames)
+    e.set_host_slices(False)
+    b = e.run_sequence(frames)
+    e.set_host_slices(True)
+    c = e.run_sequence(frames)
+    e.close()
+    assert np.array_equal(bits(a), bits(b)) and np.array_equal(bits(a), bits(c))
