@@ -245,11 +245,17 @@ int dis_pool_create(const dis_params* p, const int* devices, int n_devices, dis_
     if (r && !rc) { rc = r; err = "GPU " + std::to_string(w->device) + ": " + w->err; }
   }
   if (rc) { dis_pool_destroy(pool); return pfail(rc, err); }
-  for (Worker* w : pool->w) {   // engines that share a GPU hide each other's copies: no output slices (each costs a launch tail)
-    int same = 0;
-    for (Worker* v : pool->w) same += v->device == w->device;
-    if (same > 1) dis_set_host_slices(w->eng, 0);
-  }
+  // Engines that share a GPU hide each other's copies, so the output slices of the host-buffer calls (each costs a launch
+  // tail) gain nothing in the steady state: 30.6 against 31.0 ms per step on one B200.  They stay ON all the same: a run
+  // of K steps ends with one download nothing hides, and a quarter of the flows instead of all of them is 0.3 ms against
+  // 1.6 ms per step at K = 10 on a box whose eight GPUs share the host links (11 GB/s per GPU).  DIS_POOL_NO_SLICES=1 turns
+  // them off for long runs on fast links.
+  if (getenv("DIS_POOL_NO_SLICES"))
+    for (Worker* w : pool->w) {
+      int same = 0;
+      for (Worker* v : pool->w) same += v->device == w->device;
+      if (same > 1) dis_set_host_slices(w->eng, 0);
+    }
   *out = pool;
   return DIS_OK;
 }
