@@ -246,11 +246,10 @@ int dis_pool_create(const dis_params* p, const int* devices, int n_devices, dis_
   }
   if (rc) { dis_pool_destroy(pool); return pfail(rc, err); }
   // Engines that share a GPU hide each other's copies, so the output slices of the host-buffer calls (each costs a launch
-  // tail) gain nothing in the steady state: 30.6 against 31.0 ms per step on one B200.  They stay ON all the same: a run
-  // of K steps ends with one download nothing hides, and a quarter of the flows instead of all of them is 0.3 ms against
-  // 1.6 ms per step at K = 10 on a box whose eight GPUs share the host links (11 GB/s per GPU).  DIS_POOL_NO_SLICES=1 turns
-  // them off for long runs on fast links.
-  if (getenv("DIS_POOL_NO_SLICES"))
+  // tail at the finest level) only cost GPU time: 31.1 against 32.0 ms per 49-pair step on one B200 (bench.py, 10 steps).
+  // What stays exposed without them is the last download of a run (3 ms at 57 GB/s, 15 ms where eight GPUs share the
+  // host links at 11 GB/s): DIS_POOL_SLICES=1 keeps the slices for short runs on slow links.
+  if (!getenv("DIS_POOL_SLICES"))
     for (Worker* w : pool->w) {
       int same = 0;
       for (Worker* v : pool->w) same += v->device == w->device;
