@@ -82,6 +82,7 @@ struct Tuning {
   int conv_slack;        // DIS_CONV_SLACK        ... with at most this many unsettled patches
   float early_step;      // DIS_EARLY_STEP        k_converge -> k_stragglers when the last passes still move by this much (px)
   long long strag_wide;  // DIS_STRAG_WIDE        launches below this many patches use 8 lanes per straggler
+  int strag_dense;       // DIS_STRAG_DENSE       launches of at least this many pairs use the three-blocks-per-SM build of k_stragglers (ps 8)
   int share;             // DIS_SHARE             concurrent pair groups size their persistent grids to 1/groups of the GPU
   int groups;            // DIS_GROUPS            pair groups on concurrent streams (default 1)
   int side_blocks;       // DIS_SIDE_BLOCKS       blocks per SM of the k_stragglers launch that runs beside the walk (0: after it)

@@ -1058,9 +1058,17 @@ constexpr float kEarlyStep = 0.3f;   // px; measured on the bench workload: 0.1 
 constexpr int kTile = 19, kTileStride = 20, kTileMargin = 5;   // 9-tap window + 2 * (ceil(outlierthresh) + 1)
 constexpr int kStragWarps = 4;
 constexpr long long kYieldGraceCycles = 20000;   // ~10 us: the walk's blocks announce themselves within a few us of their launch
-__host__ __device__ constexpr int strag_min_blocks(int ps) { return (ps == 10 || ps == 12) ? DIS_BIG_BLOCKS : 1; }
-template <int PS, int SG, bool FAST>
-__global__ void __launch_bounds__(kStragWarps * 32, strag_min_blocks(PS)) k_stragglers(const SearchArgs A) {
+// ps 8 is built twice: unconstrained (170 registers, two blocks per SM: the shortest chain per pass, which is what bounds a
+// launch with few stragglers) and DENSE (three blocks per SM: ptxas then finds 136 registers without spilling; +50 %
+// resident patches, which is what bounds a launch of many pairs: 31.4 -> 30.4 ms per 49-pair step, but 3.5 -> 3.8 ms
+// for a single pair, so launch_ps picks by the number of pairs).
+constexpr int kStragDenseBlocks = 3;
+constexpr int kStragDensePairs = 16;   // DIS_STRAG_DENSE overrides (pairs per launch from which the dense build is used)
+__host__ __device__ constexpr int strag_min_blocks(int ps, bool dense) {
+  return (ps == 10 || ps == 12) ? DIS_BIG_BLOCKS : (ps == 8 && dense ? kStragDenseBlocks : 1);
+}
+template <int PS, int SG, bool FAST, bool DENSE = false>
+__global__ void __launch_bounds__(kStragWarps * 32, strag_min_blocks(PS, DENSE)) k_stragglers(const SearchArgs A) {
   using G = Geom<PS, SG>;
   extern __shared__ float tiles[];
   const int th = A.height + 2 * A.pad;
@@ -1255,6 +1263,10 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
     const size_t tsm_n = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SG>::G * kTile * kTileStride : 0;
     cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm_n);
     cudaFuncSetAttribute(k_stragglers<PS, SG, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if constexpr (PS == 8) {
+      cudaFuncSetAttribute(k_stragglers<PS, SG, FAST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm_n);
+      cudaFuncSetAttribute(k_stragglers<PS, SG, FAST, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    }
   }
   // persistent warps: lanes fetch patches from a global counter until the level is done
   if (a.band_h <= 0) { a.band_y0 = 0; a.band_h = a.nph; }
@@ -1286,6 +1298,9 @@ int launch_ps(const SearchArgs& a_in, cudaStream_t s, cudaEvent_t* ev, const Sea
       k_stragglers<PS, WS, FAST><<<nblocks, kStragWarps * 32, tsm, st>>>(a);
     } else {
       const size_t tsm = PS == 8 ? sizeof(float) * kStragWarps * Geom<PS, SG>::G * kTile * kTileStride : 0;
+      if constexpr (PS == 8) {
+        if (a.n_pairs >= tn.strag_dense) { k_stragglers<PS, SG, FAST, true><<<nblocks, kStragWarps * 32, tsm, st>>>(a); return; }
+      }
       k_stragglers<PS, SG, FAST><<<nblocks, kStragWarps * 32, tsm, st>>>(a);
     }
   };
@@ -1349,6 +1364,7 @@ Tuning parse_tuning() {
     t.conv_slack = (e = getenv("DIS_CONV_SLACK")) ? atoi(e) : 2;
     t.early_step = (e = getenv("DIS_EARLY_STEP")) ? (float)atof(e) : kEarlyStep;
     t.strag_wide = (e = getenv("DIS_STRAG_WIDE")) ? atoll(e) : kStragWideBelow;
+    t.strag_dense = (e = getenv("DIS_STRAG_DENSE")) ? atoi(e) : kStragDensePairs;
     t.share = getenv("DIS_SHARE") ? 1 : 0;
     t.groups = (e = getenv("DIS_GROUPS")) ? (atoi(e) > 1 ? atoi(e) : 1) : 1;
     t.side_blocks = (e = getenv("DIS_SIDE_BLOCKS")) ? (atoi(e) > 0 ? atoi(e) : 0) : 4;

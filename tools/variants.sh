@@ -9,7 +9,7 @@ SRC=optical-flow-using-dense-inverse-search_b200/csrc
 for spec in "$@"; do
   name="${spec%%=*}"; flags="${spec#*=}"
   ( nvcc $flags -gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo -fmad=false -prec-div=true -prec-sqrt=true \
-      -ftz=false -Xcompiler -fPIC,-fvisibility=hidden -shared -o tools/variants/$name.so \
+      -ftz=false -Xcompiler -fPIC,-fvisibility=hidden -Xptxas -v -shared -o tools/variants/$name.so \
       $SRC/dis_api.cu $SRC/dis_search.cu $SRC/dis_densify.cu $SRC/dis_pyramid.cu $SRC/dis_color.cu $SRC/dis_pool.cu $SRC/dis_noalloc.cu -lpthread 2> tools/variants/$name.log && echo "built $name ($flags)" ) &
 done
 wait
