@@ -57,6 +57,26 @@ def test_sliced_batch_equals_single_pairs(seq):
     assert np.array_equal(bits(out), bits(alone))
 
 
+@pytest.mark.parametrize("dense_from", [1, 1000000])
+def test_both_builds_of_k_stragglers_agree(seq, dense_from):
+    """ps 8 has two builds of k_stragglers (two or three blocks per SM, csrc/dis_search.cu); launch_ps picks by the number
+    of pairs in the launch (DIS_STRAG_DENSE).  Forced either way, a 40-pair run equals the pairs run alone."""
+    frames, alone = seq
+    tune("DIS_STRAG_DENSE", dense_from)
+    try:
+        e = dis_b200.Engine(0)
+        first = np.arange(40, dtype=np.int32)
+        e.upload_frames(frames, first, first + 1)
+        e.run_resident()
+        out = e.download_flows()
+        one = e.run_pair(frames[3], frames[4])
+        e.close()
+    finally:
+        tune("DIS_STRAG_DENSE", None)
+    assert np.array_equal(bits(out), bits(alone))
+    assert np.array_equal(bits(one), bits(alone[3]))
+
+
 def test_chunked_sequence_of_130_frames():
     """> 128 pairs: dis_run_sequence_u8 works in chunks of 128 pairs; the last chunk here has one pair."""
     frames, _ = dis_b200.synth.make_sequence(131, 64, 48, seed=12)
