@@ -69,7 +69,7 @@ def test_noalloc_colour_allocates_nothing():
         E.color_code_device_noalloc(dev, di.data_ptr(), w, h, do.data_ptr())
     torch.cuda.synchronize(dev)
     free1, _ = torch.cuda.mem_get_info(dev)
-    assert free1 == free0
+    assert free1 >= free0          # nothing was taken from the device between the two readings
 
 
 def test_noalloc_colour_rejects_bad_sizes():
